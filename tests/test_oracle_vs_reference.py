@@ -1,0 +1,56 @@
+"""CPU, build container only: oracle/restate.py against the real reference imported live.
+
+Skipped wherever /root/reference is not mounted (e.g. the GPU box); the committed
+tests/golden fixtures cover the same comparison there.
+"""
+import numpy as np
+import pytest
+
+from oracle import ref_shim, restate, synth
+
+pytestmark = pytest.mark.skipif(not ref_shim.available(), reason="reference tree not mounted")
+
+
+@pytest.fixture(scope="module")
+def R():
+    return ref_shim.ref()
+
+
+@pytest.mark.parametrize("seed", [10, 11])
+def test_nms_live(R, seed):
+    for dt, th in [(np.float64, 0.3), (np.float32, 0.7)]:
+        dets = synth.class_dets(seed, n=400, dtype=dt)
+        assert restate.nms(dets, th) == [int(i) for i in R.nms(dets, th)]
+
+
+def test_overlaps_live(R):
+    gt = synth.gt_boxes(3, G=5).astype(np.float64)
+    rois = synth.jittered_rois(3, gt.astype(np.float32), R=120)[:, 1:5].astype(np.float64)
+    want = R.bbox_overlaps(rois, gt)
+    assert np.array_equal(restate.bbox_overlaps(rois, gt), want)
+    assert np.array_equal(restate.bbox_overlaps_loop(rois, gt), want)
+
+
+@pytest.mark.parametrize("seed", [20, 21])
+def test_assign_anchor_live(R, seed):
+    gt = synth.gt_boxes(seed, G=5, im_h=300, im_w=500)
+    info = np.array([[300, 500, 0.8]], np.float32)
+    np.random.seed(seed)
+    want = R.assign_anchor((1, 18, 19, 31), gt, info)
+    got = restate.assign_anchor((1, 18, 19, 31), gt, info, rng=np.random.RandomState(seed))
+    for k in want:
+        assert np.array_equal(want[k], got[k]), k
+
+
+def test_sample_rois_live(R):
+    gt = synth.gt_boxes(5, G=4)
+    rois = np.vstack((synth.jittered_rois(5, gt, R=500), np.hstack((np.zeros((4, 1), np.float32), gt[:, :4]))))
+    R.config.TRAIN.BG_THRESH_LO = 0.0
+    np.random.seed(5)
+    want = R._sample_rois(rois, gt, 32, 128, 21, "TRAIN")
+    R.config.TRAIN.BG_THRESH_LO = 0.1
+    cfg = restate.default_config()
+    cfg.TRAIN.BG_THRESH_LO = 0.0
+    got = restate.sample_rois_e2e(rois, gt, 32, 128, 21, "TRAIN", cfg=cfg, rng=np.random.RandomState(5))
+    for a, b in zip(want, got):
+        assert np.array_equal(a, b)
