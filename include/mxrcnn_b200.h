@@ -1,0 +1,144 @@
+/*
+ * mxrcnn_b200.h -- C ABI of libmxrcnn_b200.so
+ *
+ * B200 (sm_100a) implementation of the RPN proposal / box-processing hot path of
+ * walkoncross/mx-rcnn.  The reference has no native code and no FFI on this path (it is
+ * numpy inside MXNet CustomOp callbacks), so each entry point cites the reference
+ * PYTHON function (file:line under the reference root) whose work it replaces; the
+ * Python host layer in mxrcnn_b200/ binds these with ctypes and mirrors the reference's
+ * own signatures.  INTEGRATION.md shows the reference-side stubs.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative mxr_status; the text of the
+ *     last error of the calling thread is returned by mxr_last_error_string().
+ *   - "dev" pointers are device pointers on the handle's device; "host" pointers are
+ *     host pointers.  The caller owns every in/out buffer.  The library owns only the
+ *     handle's workspace (device scratch + pinned staging), which grows on demand in
+ *     mxr_reserve_*() -- call those at set-up to keep allocations out of the hot call.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the handle's own stream).
+ *     Device-pointer calls only enqueue work and never synchronise.  *_host calls
+ *     copy in, compute, copy out and return after the results are in the host buffers.
+ *   - a handle is bound to one device and is not thread-safe; use one per thread/stream.
+ *   - no random numbers are drawn inside the library: sampling entry points take the
+ *     permutations / draws from the caller (the reference uses numpy's global RNG).
+ *   - layouts and dtypes are the reference's: NCHW f32 maps,
+ *     boxes [x1,y1,x2,y2] with inclusive pixel coordinates (+1 widths), f64 box math.
+ */
+#ifndef MXRCNN_B200_H_
+#define MXRCNN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mxr_handle_s* mxr_handle_t;
+
+typedef enum {
+  MXR_OK = 0,
+  MXR_ERR_INVALID = -1,   /* bad argument                          -> ValueError   */
+  MXR_ERR_CUDA = -2,      /* CUDA runtime failure                  -> RuntimeError */
+  MXR_ERR_NAN = -3,       /* NaN in scores/deltas (proposal.py:58-62) -> ValueError */
+  MXR_ERR_LIMIT = -4,     /* size beyond a documented maximum      -> ValueError   */
+  MXR_ERR_NOMEM = -5,     /* allocation failed                     -> MemoryError  */
+  MXR_ERR_EMPTY = -6      /* empty candidate set where the reference raises (Q7) */
+} mxr_status;
+
+#define MXR_DTYPE_F32 0
+#define MXR_DTYPE_F64 1
+
+const char* mxr_last_error_string(void);
+int mxr_version(void);
+
+/* ---- handle ------------------------------------------------------------------------ */
+int mxr_create(int device, mxr_handle_t* out);
+int mxr_destroy(mxr_handle_t h);
+/* Bytes of device workspace currently held by the handle. */
+size_t mxr_workspace_bytes(mxr_handle_t h);
+/* Wait for everything enqueued on `stream` (NULL = handle stream). */
+int mxr_synchronize(mxr_handle_t h, void* stream);
+
+/* Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg;
+ * the reference's only instrumentation is the Speedometer log, rcnn/callback.py:14-36).
+ * enable(1) starts recording every kernel launch of this handle; read() synchronises the device,
+ * sums milliseconds and launch counts per stage id (< max_stages) and clears the records. */
+int mxr_profile_enable(mxr_handle_t h, int on);
+int mxr_profile_read(mxr_handle_t h, int max_stages, double* total_ms, int32_t* counts);
+const char* mxr_profile_stage_name(int stage);
+/* Kernels launched by the most recent call on this handle. */
+int mxr_last_launch_count(mxr_handle_t h);
+
+/* ---- A0  helper/processing/generate_anchor.py:8-72 ---------------------------------- */
+/* Host-side constant table (<= 64 rows); out_anchors: host, (n_ratios*n_scales, 4) f64,
+ * ratio-major / scale-minor row order. */
+int mxr_generate_anchors(double base_size, const double* ratios, int n_ratios, const double* scales, int n_scales,
+                         double* out_anchors);
+
+/* ---- A1  rcnn/rpn/proposal.py:39-149  ProposalOperator.forward ---------------------- */
+typedef struct {
+  int batch;            /* B images (the reference supports 1: proposal.py:195-196)          */
+  int num_anchors;      /* A                                                                 */
+  int height, width;    /* H, W of the score / delta maps                                    */
+  int crop_h, crop_w;   /* proposal.py:70-71 TRAIN-mode crop; <=0 or >=H/W means no crop     */
+  double feat_stride;   /* proposal.py:22                                                    */
+  int pre_nms_top_n;    /* <=0: keep all (proposal.py:124)                                   */
+  int post_nms_top_n;   /* <=0: keep all NMS survivors (proposal.py:132); output rows = this */
+  double nms_thresh;    /* python float                                                      */
+  float min_size;       /* RPN_MIN_SIZE; multiplied by im_info[2] in f32 (NEP 50)            */
+  int first_stripe;     /* tuning: width of the first NMS stripe (0 = automatic)             */
+} mxr_proposal_params;
+
+/* Size the workspace for a configuration (optional; forward calls reserve on demand). */
+int mxr_reserve_proposal(mxr_handle_t h, const mxr_proposal_params* p);
+
+/*
+ * cls_prob  dev (B, 2A, H, W) f32   only the foreground half [A:2A) is read
+ * bbox_pred dev (B, 4A, H, W) f32
+ * im_info   dev (B, 3) f32          [height, width, scale]
+ * anchors   HOST (A, 4) f64         from mxr_generate_anchors
+ * out_rois  dev (B, post, 5) f32    [batch_index, x1, y1, x2, y2]; rows >= nkeep are zero
+ * out_scores dev (B, post) f32 or NULL
+ * out_keep  dev (B, post) i32 or NULL   index into the sorted pre-NMS list (the reference's `keep`)
+ * out_anchor_index dev (B, post) i32 or NULL   (h,w,a)-order row of the kept proposal
+ * out_nkeep dev (B, 2) i32          [nkeep, flags]; flags bit0 = NaN seen in inputs
+ * When post_nms_top_n <= 0 the row capacity of the outputs is `out_capacity` per image.
+ * Rows beyond nkeep are padded by the caller (proposal.py:135-139 draws from numpy's RNG):
+ * see mxr_proposal_pad.
+ */
+int mxr_proposal_forward(mxr_handle_t h, void* stream, const mxr_proposal_params* p, const float* cls_prob,
+                         const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
+                         float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
+                         int32_t* out_nkeep);
+
+/* Same, all pointers HOST; returns MXR_ERR_NAN like the reference's ValueError. */
+int mxr_proposal_forward_host(mxr_handle_t h, const mxr_proposal_params* p, const float* cls_prob,
+                              const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
+                              float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
+                              int32_t* out_nkeep);
+
+/* proposal.py:135-139: rows [nkeep, nkeep+n_pad) of image `image` := row pad_rows[t] (< nkeep).
+ * pad_rows: HOST, drawn by the caller as randint(0, nkeep, n_pad). */
+int mxr_proposal_pad(mxr_handle_t h, void* stream, int image, int rows_per_image, int nkeep, const int32_t* pad_rows,
+                     int n_pad, float* out_rois, float* out_scores);
+
+/* ---- A5  helper/processing/nms.py:4-38  nms(dets, thresh) ---------------------------- */
+/* dets dev (n,5) [x1,y1,x2,y2,score] f32 or f64 (arithmetic in that dtype, like numpy);
+ * sorts by descending score (ties: higher index first), greedy-suppresses IoU > thresh.
+ * keep_out dev (n) i32: original row indices in keep order; nkeep_out dev (2) i32.
+ * max_keep > 0 stops after that many (prefix of the full result). */
+int mxr_nms(mxr_handle_t h, void* stream, const void* dets, int n, int dtype, double thresh, int max_keep,
+            int32_t* keep_out, int32_t* nkeep_out);
+int mxr_nms_host(mxr_handle_t h, const void* dets, int n, int dtype, double thresh, int max_keep, int32_t* keep_out,
+                 int32_t* nkeep_out);
+/* Batched form for the per-class loop of rcnn/tester.py:50-56: problem c owns rows
+ * [offsets[c], offsets[c+1]) of dets; keep_out rows are problem-local indices written at
+ * keep_out + offsets[c]; nkeep_out (n_problems, 2).  offsets: HOST (n_problems+1). */
+int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_t* offsets, int n_problems, int dtype,
+                    double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MXRCNN_B200_H_ */

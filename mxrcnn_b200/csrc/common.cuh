@@ -1,0 +1,128 @@
+// Shared declarations for libmxrcnn_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "mxrcnn_b200.h"
+
+namespace mxr {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+void set_error(const char* fmt, ...);
+
+#define MXR_CUDA(expr)                                                                                       \
+  do {                                                                                                       \
+    cudaError_t e_ = (expr);                                                                                 \
+    if (e_ != cudaSuccess) {                                                                                 \
+      mxr::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__);            \
+      return MXR_ERR_CUDA;                                                                                   \
+    }                                                                                                        \
+  } while (0)
+
+#define MXR_REQUIRE(cond, code, ...)  \
+  do {                                \
+    if (!(cond)) {                    \
+      mxr::set_error(__VA_ARGS__);    \
+      return (code);                  \
+    }                                 \
+  } while (0)
+
+#define MXR_TRY(expr)          \
+  do {                         \
+    int s_ = (expr);           \
+    if (s_ != MXR_OK) return s_; \
+  } while (0)
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline int round_up_int(int v, int a) { return (v + a - 1) / a * a; }
+static inline int pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// Per-problem (image / class) control block, zeroed at the start of every call.
+struct Ctrl {
+  int n_valid;   // decode: boxes that pass the min-size filter
+  int nan_flag;  // decode / prepare: NaN seen in the inputs
+  int n;         // boxes entering NMS (after top-k)
+  int nkept;     // scan: boxes kept so far
+  int done;      // scan: problem finished (post-NMS quota reached or list exhausted)
+  int pad[3];
+};
+
+// Kernel stages, for the optional per-kernel CUDA-event profile (mxr_profile_*).
+enum Stage {
+  ST_MEMSET = 0,
+  ST_DECODE = 1,
+  ST_TOPK = 2,
+  ST_NMS_STRIPE = 3,
+  ST_NMS_SCAN = 4,
+  ST_NMS_PREP = 5,
+  ST_BOXES = 6,
+  ST_OVERLAPS = 7,
+  ST_ANCHOR_TARGET = 8,
+  ST_PROPOSAL_TARGET = 9,
+  ST_COUNT = 10
+};
+
+struct ProfRec {
+  cudaEvent_t a, b;
+  int stage;
+};
+
+struct Handle {
+  int device;
+  cudaStream_t stream;
+  char* d_ws;
+  size_t d_bytes;
+  char* h_pin;
+  size_t h_bytes;
+  cudaEvent_t ev;
+  // profiling (off by default: no events are recorded in the hot path)
+  int prof_on;
+  ProfRec* prof;
+  int prof_cap, prof_used;
+  int last_launches;  // kernels launched by the most recent call
+};
+
+// Bracket one kernel launch.  No-ops unless mxr_profile_enable(h, 1) was called.
+static inline void prof_begin(Handle* h, cudaStream_t s, int stage) {
+  h->last_launches++;
+  if (!h->prof_on || h->prof_used >= h->prof_cap) return;
+  ProfRec& r = h->prof[h->prof_used];
+  r.stage = stage;
+  cudaEventRecord(r.a, s);
+}
+static inline void prof_end(Handle* h, cudaStream_t s) {
+  if (!h->prof_on || h->prof_used >= h->prof_cap) return;
+  cudaEventRecord(h->prof[h->prof_used].b, s);
+  h->prof_used++;
+}
+
+// Grow-only workspaces.  Growth synchronises the device (never in steady state).
+int ensure_device_ws(Handle* h, size_t bytes);
+int ensure_pinned_ws(Handle* h, size_t bytes);
+
+// Bump allocator over the handle's device workspace.
+struct Carver {
+  char* base;
+  size_t off;
+  explicit Carver(char* b) : base(b), off(0) {}
+  template <typename T>
+  T* take(size_t count) {
+    off = align_up(off, 256);
+    T* p = reinterpret_cast<T*>(base ? base + off : nullptr);
+    off += count * sizeof(T);
+    return p;
+  }
+};
+
+struct AnchorTable {
+  double a[64][4];
+};
+
+}  // namespace mxr

@@ -1,0 +1,274 @@
+// helper/processing/nms.py:4-38 -- nms(dets, thresh), single and batched (per-class) forms.
+#include <string.h>
+
+#include "nms_host.cuh"
+#include "sort.cuh"
+
+using namespace mxr;
+
+namespace {
+
+const int kSmemSortMax = 16384;
+
+template <typename T>
+struct PrepArrays {
+  typename Ar<T>::Box* box;
+  T* area;
+  int* orig;
+  int cap;
+  u64* g_sort_keys;
+  u32* g_sort_pl;
+  int g_sort_cap;
+};
+
+template <typename T>
+__device__ __forceinline__ u64 det_key(T s);
+template <>
+__device__ __forceinline__ u64 det_key<float>(float s) { return (u64)score_key32(s) << 32; }
+template <>
+__device__ __forceinline__ u64 det_key<double>(double s) { return score_key64(s); }
+
+// One CTA per problem: order = scores.argsort()[::-1] (nms.py:19; ties: higher index first),
+// then boxes / areas (nms.py:18) are gathered into processing order.
+template <typename T>
+__global__ void __launch_bounds__(1024) nms_prepare_kernel(const T* __restrict__ dets, const int* __restrict__ offsets,
+                                                           PrepArrays<T> pa, int n_pow2_max, int use_smem_sort,
+                                                           Ctrl* __restrict__ ctrl) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int row0 = offsets[b];
+  const int n = offsets[b + 1] - row0;
+  if (tid == 0) ctrl[b].n = n;
+  if (n <= 0) return;
+  const T* d = dets + (size_t)row0 * 5;
+  const int n_pow2 = max(2, (int)(1u << (32 - __clz(n - 1))));
+  u64* skeys;
+  u32* spl;
+  if (use_smem_sort) {
+    skeys = reinterpret_cast<u64*>(smem_raw);
+    spl = reinterpret_cast<u32*>(smem_raw + (size_t)n_pow2_max * 8);
+  } else {
+    skeys = pa.g_sort_keys + (size_t)b * pa.g_sort_cap;
+    spl = pa.g_sort_pl + (size_t)b * pa.g_sort_cap;
+  }
+  bool nan = false;
+  for (int i = tid; i < n_pow2; i += blockDim.x) {
+    if (i < n) {
+      const T s = d[(size_t)i * 5 + 4];
+      nan = nan || (s != s);
+      skeys[i] = det_key<T>(s);
+      spl[i] = (u32)i + 1u;  // +1 keeps every real pair above the (0,0) padding
+    } else {
+      skeys[i] = 0;
+      spl[i] = 0;
+    }
+  }
+  __syncthreads();
+  bitonic_sort_desc(skeys, spl, n_pow2);
+  for (int i = tid; i < n; i += blockDim.x) {
+    const int src = (int)spl[i] - 1;
+    const T x1 = d[(size_t)src * 5], y1 = d[(size_t)src * 5 + 1], x2 = d[(size_t)src * 5 + 2], y2 = d[(size_t)src * 5 + 3];
+    nan = nan || (x1 != x1) || (y1 != y1) || (x2 != x2) || (y2 != y2);
+    const size_t o = (size_t)b * pa.cap + i;
+    typename Ar<T>::Box bx;
+    bx.x = x1;
+    bx.y = y1;
+    bx.z = x2;
+    bx.w = y2;
+    pa.box[o] = bx;
+    pa.area[o] = box_area<T>(x1, y1, x2, y2);
+    pa.orig[o] = src;
+  }
+  if (__syncthreads_or(nan) && tid == 0) ctrl[b].nan_flag = 1;
+}
+
+struct NmsLayout {
+  int P, n_max, cap, keep_cap, n_pow2_max, use_smem_sort;
+  StripePlan plan;
+  Ctrl* ctrl;
+  u64* R;
+  size_t zero_bytes;
+  int* offsets;
+  void* box;
+  void* area;
+  int* orig;
+  int* kept_slot;
+  u64* M;
+  u64* g_sort_keys;
+  u32* g_sort_pl;
+  // host-io staging
+  void* d_dets;
+  int* d_keep;
+  int* d_nkeep;
+  size_t total;
+};
+
+void make_layout(int P, int n_max, int n_total, int max_keep, size_t esize, bool host_io, char* base, NmsLayout* L) {
+  L->P = P;
+  L->n_max = n_max;
+  L->cap = round_up_int(n_max < 1 ? 1 : n_max, 64);
+  L->keep_cap = (max_keep > 0 && max_keep < n_max) ? max_keep : (n_max < 1 ? 1 : n_max);
+  L->n_pow2_max = pow2_ceil(n_max < 2 ? 2 : n_max);
+  L->use_smem_sort = L->n_pow2_max <= kSmemSortMax;
+  L->plan = plan_stripes(n_max, max_keep > 0 ? L->keep_cap : 0, 0);
+  Carver c(base);
+  L->ctrl = c.take<Ctrl>(P);
+  L->R = c.take<u64>((size_t)P * (L->cap / 64));
+  L->zero_bytes = c.off;
+  L->offsets = c.take<int>(P + 1);
+  L->box = c.take<char>((size_t)P * L->cap * 4 * esize);
+  L->area = c.take<char>((size_t)P * L->cap * esize);
+  L->orig = c.take<int>((size_t)P * L->cap);
+  L->kept_slot = c.take<int>((size_t)P * L->keep_cap);
+  L->M = c.take<u64>((size_t)P * L->plan.max_width * (L->plan.max_width / 64));
+  if (!L->use_smem_sort) {
+    L->g_sort_keys = c.take<u64>((size_t)P * L->n_pow2_max);
+    L->g_sort_pl = c.take<u32>((size_t)P * L->n_pow2_max);
+  } else {
+    L->g_sort_keys = nullptr;
+    L->g_sort_pl = nullptr;
+  }
+  if (host_io) {
+    L->d_dets = c.take<char>((size_t)(n_total < 1 ? 1 : n_total) * 5 * esize);
+    L->d_keep = c.take<int>(n_total < 1 ? 1 : n_total);
+    L->d_nkeep = c.take<int>((size_t)P * 2);
+  }
+  L->total = align_up(c.off, 256);
+}
+
+template <typename T>
+int enqueue_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets, double thresh, int max_keep, int32_t* keep_out,
+              int32_t* nkeep_out) {
+  PrepArrays<T> pa;
+  pa.box = reinterpret_cast<typename Ar<T>::Box*>(L.box);
+  pa.area = reinterpret_cast<T*>(L.area);
+  pa.orig = L.orig;
+  pa.cap = L.cap;
+  pa.g_sort_keys = L.g_sort_keys;
+  pa.g_sort_pl = L.g_sort_pl;
+  pa.g_sort_cap = L.n_pow2_max;
+  size_t smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 12 : 16;
+  MXR_CUDA(cudaFuncSetAttribute(nms_prepare_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  prof_begin(h, s, ST_NMS_PREP);
+  nms_prepare_kernel<T><<<L.P, 1024, smem, s>>>(dets, L.offsets, pa, L.n_pow2_max, L.use_smem_sort, L.ctrl);
+  prof_end(h, s);
+  NmsArrays<T> na;
+  na.box = pa.box;
+  na.area = pa.area;
+  na.score = nullptr;
+  na.orig = L.orig;
+  na.cap = L.cap;
+  na.M = L.M;
+  na.m_pitch = L.plan.max_width / 64;
+  na.m_stride = (size_t)L.plan.max_width * na.m_pitch;
+  na.R = L.R;
+  na.r_words = L.cap / 64;
+  na.kept_slot = L.kept_slot;
+  na.keep_cap = L.keep_cap;
+  NmsOutputs o;
+  o.rois = nullptr;
+  o.scores = nullptr;
+  o.keep_pos = nullptr;
+  o.keep_orig = keep_out;
+  o.nkeep = nkeep_out;
+  o.rows = 0;
+  o.row_offsets = L.offsets;
+  // numpy compares `ovr <= thresh` in the dtype of dets: a python float is cast to f32
+  // for f32 dets (NEP 50 weak scalar; value-based casting before numpy 2 agrees)
+  return run_nms_stripes<T>(h, s, L.ctrl, na, o, L.P, L.n_max, max_keep > 0 ? L.keep_cap : 0, L.plan, (T)thresh);
+}
+
+// offsets: HOST array of P+1 ints.
+int run(Handle* h, cudaStream_t s, const void* dets, bool dets_on_host, const int32_t* offsets, int P, int dtype,
+        double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out) {
+  MXR_REQUIRE(dtype == MXR_DTYPE_F32 || dtype == MXR_DTYPE_F64, MXR_ERR_INVALID, "nms: dtype must be f32 or f64");
+  MXR_REQUIRE(P >= 1 && offsets != nullptr && nkeep_out != nullptr, MXR_ERR_INVALID, "nms: bad problem list");
+  int n_max = 0;
+  for (int i = 0; i < P; ++i) {
+    MXR_REQUIRE(offsets[i + 1] >= offsets[i], MXR_ERR_INVALID, "nms: offsets must be non-decreasing");
+    if (offsets[i + 1] - offsets[i] > n_max) n_max = offsets[i + 1] - offsets[i];
+  }
+  const int n_total = offsets[P] - offsets[0];
+  MXR_REQUIRE(offsets[0] == 0, MXR_ERR_INVALID, "nms: offsets[0] must be 0");
+  MXR_REQUIRE(n_total == 0 || (dets != nullptr && keep_out != nullptr), MXR_ERR_INVALID, "nms: NULL dets/keep");
+  MXR_REQUIRE(n_max <= (1 << 24), MXR_ERR_LIMIT, "nms: %d boxes in one problem exceeds the maximum of 16777216", n_max);
+  const size_t esize = dtype == MXR_DTYPE_F64 ? 8 : 4;
+  NmsLayout L;
+  make_layout(P, n_max, n_total, max_keep, esize, dets_on_host, nullptr, &L);
+  MXR_TRY(ensure_device_ws(h, L.total));
+  make_layout(P, n_max, n_total, max_keep, esize, dets_on_host, h->d_ws, &L);
+  const size_t off_bytes = (size_t)(P + 1) * sizeof(int);
+  const size_t pin_need = off_bytes + (dets_on_host ? ((size_t)n_total + 2 * (size_t)P) * sizeof(int) : 0);
+  MXR_TRY(ensure_pinned_ws(h, pin_need));
+  MXR_CUDA(cudaStreamSynchronize(s));  // the pinned block may still feed an earlier copy
+  memcpy(h->h_pin, offsets, off_bytes);
+  h->last_launches = 0;
+  MXR_CUDA(cudaMemsetAsync(L.ctrl, 0, L.zero_bytes, s));
+  MXR_CUDA(cudaMemcpyAsync(L.offsets, h->h_pin, off_bytes, cudaMemcpyHostToDevice, s));
+  const void* d_dets = dets;
+  int32_t* d_keep = keep_out;
+  int32_t* d_nkeep = nkeep_out;
+  if (dets_on_host) {
+    if (n_total > 0) MXR_CUDA(cudaMemcpyAsync(L.d_dets, dets, (size_t)n_total * 5 * esize, cudaMemcpyHostToDevice, s));
+    d_dets = L.d_dets;
+    d_keep = L.d_keep;
+    d_nkeep = L.d_nkeep;
+  }
+  if (dtype == MXR_DTYPE_F64) {
+    MXR_TRY(enqueue_t<double>(h, s, L, reinterpret_cast<const double*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+  } else {
+    MXR_TRY(enqueue_t<float>(h, s, L, reinterpret_cast<const float*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+  }
+  if (dets_on_host) {
+    char* hp = h->h_pin + off_bytes;
+    if (n_total > 0) MXR_CUDA(cudaMemcpyAsync(hp, d_keep, (size_t)n_total * sizeof(int), cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpyAsync(hp + (size_t)n_total * sizeof(int), d_nkeep, (size_t)P * 2 * sizeof(int),
+                             cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaStreamSynchronize(s));
+    if (n_total > 0) memcpy(keep_out, hp, (size_t)n_total * sizeof(int));
+    memcpy(nkeep_out, hp + (size_t)n_total * sizeof(int), (size_t)P * 2 * sizeof(int));
+    for (int i = 0; i < P; ++i) {
+      if (nkeep_out[i * 2 + 1] & 1) {
+        set_error("nms: NaN in dets (problem %d); the reference's result for NaN input is not defined", i);
+        return MXR_ERR_NAN;
+      }
+    }
+  }
+  return MXR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mxr_nms(mxr_handle_t hh, void* stream, const void* dets, int n, int dtype, double thresh, int max_keep,
+            int32_t* keep_out, int32_t* nkeep_out) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms: NULL handle");
+  MXR_REQUIRE(n >= 0, MXR_ERR_INVALID, "mxr_nms: n < 0");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  const int32_t offs[2] = {0, n};
+  return run(h, stream ? (cudaStream_t)stream : h->stream, dets, false, offs, 1, dtype, thresh, max_keep, keep_out,
+             nkeep_out);
+}
+
+int mxr_nms_host(mxr_handle_t hh, const void* dets, int n, int dtype, double thresh, int max_keep, int32_t* keep_out,
+                 int32_t* nkeep_out) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms_host: NULL handle");
+  MXR_REQUIRE(n >= 0, MXR_ERR_INVALID, "mxr_nms_host: n < 0");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  const int32_t offs[2] = {0, n};
+  return run(h, h->stream, dets, true, offs, 1, dtype, thresh, max_keep, keep_out, nkeep_out);
+}
+
+int mxr_nms_batched(mxr_handle_t hh, void* stream, const void* dets, const int32_t* offsets, int n_problems, int dtype,
+                    double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms_batched: NULL handle");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  return run(h, stream ? (cudaStream_t)stream : h->stream, dets, false, offsets, n_problems, dtype, thresh, max_keep,
+             keep_out, nkeep_out);
+}
+
+}  // extern "C"

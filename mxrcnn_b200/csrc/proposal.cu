@@ -1,0 +1,293 @@
+// rcnn/rpn/proposal.py:39-149 -- host side of the proposal operator.
+#include <string.h>
+
+#include "nms_host.cuh"
+#include "proposal_kernels.cuh"
+
+using namespace mxr;
+
+namespace {
+
+const int kSmemSortMax = 16384;  // pairs that fit the 227 KB of shared memory (12 B each)
+
+struct Layout {
+  // derived sizes
+  int B, A, H, W, hc, wc, n_crop, n_full, cropped;
+  int n_max, cap, keep_cap, out_rows, n_pow2_max, use_smem_sort;
+  StripePlan plan;
+  // device carve
+  Ctrl* ctrl;
+  u64* R;
+  size_t zero_bytes;  // ctrl + R are contiguous and zeroed per call
+  u32* keys;
+  double4* box;
+  double* area;
+  float* score;
+  int* orig;
+  int* kept_slot;
+  u64* M;
+  u64* g_sort_keys;
+  u32* g_sort_pl;
+  // staging for the *_host entry point
+  float* d_cls;
+  float* d_box;
+  float* d_info;
+  char* d_out;
+  size_t out_bytes, off_scores, off_keep, off_anchor, off_nkeep;
+  size_t total;
+};
+
+int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, char* base, Layout* L) {
+  MXR_REQUIRE(p != nullptr, MXR_ERR_INVALID, "proposal: params is NULL");
+  MXR_REQUIRE(p->batch >= 1 && p->num_anchors >= 1 && p->num_anchors <= 64 && p->height >= 1 && p->width >= 1,
+              MXR_ERR_INVALID, "proposal: bad shape B=%d A=%d H=%d W=%d (A must be 1..64)", p->batch, p->num_anchors,
+              p->height, p->width);
+  MXR_REQUIRE(p->feat_stride > 0, MXR_ERR_INVALID, "proposal: feat_stride must be > 0");
+  L->B = p->batch;
+  L->A = p->num_anchors;
+  L->H = p->height;
+  L->W = p->width;
+  L->hc = (p->crop_h > 0 && p->crop_h < p->height) ? p->crop_h : p->height;
+  L->wc = (p->crop_w > 0 && p->crop_w < p->width) ? p->crop_w : p->width;
+  L->cropped = (L->hc < L->H || L->wc < L->W) ? 1 : 0;
+  const long long n_crop = (long long)L->A * L->hc * L->wc, n_full = (long long)L->A * L->H * L->W;
+  MXR_REQUIRE(n_full <= (1 << 24), MXR_ERR_LIMIT, "proposal: A*H*W = %lld exceeds the maximum of 16777216", n_full);
+  L->n_crop = (int)n_crop;
+  L->n_full = (int)n_full;
+  L->n_max = (p->pre_nms_top_n > 0 && p->pre_nms_top_n < L->n_crop) ? p->pre_nms_top_n : L->n_crop;
+  L->cap = round_up_int(L->n_max, 64);
+  L->keep_cap = (p->post_nms_top_n > 0 && p->post_nms_top_n < L->n_max) ? p->post_nms_top_n : L->n_max;
+  L->out_rows = p->post_nms_top_n > 0 ? p->post_nms_top_n : out_capacity;
+  MXR_REQUIRE(L->out_rows >= 1, MXR_ERR_INVALID, "proposal: post_nms_top_n <= 0 needs out_capacity >= 1");
+  L->n_pow2_max = pow2_ceil(L->n_max < 2 ? 2 : L->n_max);
+  L->use_smem_sort = L->n_pow2_max <= kSmemSortMax;
+  L->plan = plan_stripes(L->n_max, p->post_nms_top_n > 0 ? L->keep_cap : 0, p->first_stripe);
+  Carver c(base);
+  const int r_words = L->cap / 64;
+  L->ctrl = c.take<Ctrl>(L->B);
+  L->R = c.take<u64>((size_t)L->B * r_words);
+  L->zero_bytes = c.off;
+  L->keys = c.take<u32>((size_t)L->B * L->n_crop);
+  L->box = c.take<double4>((size_t)L->B * L->cap);
+  L->area = c.take<double>((size_t)L->B * L->cap);
+  L->score = c.take<float>((size_t)L->B * L->cap);
+  L->orig = c.take<int>((size_t)L->B * L->cap);
+  L->kept_slot = c.take<int>((size_t)L->B * L->keep_cap);
+  const size_t m_words = (size_t)L->plan.max_width * (L->plan.max_width / 64);
+  L->M = c.take<u64>((size_t)L->B * m_words);
+  if (!L->use_smem_sort) {
+    L->g_sort_keys = c.take<u64>((size_t)L->B * L->n_pow2_max);
+    L->g_sort_pl = c.take<u32>((size_t)L->B * L->n_pow2_max);
+  } else {
+    L->g_sort_keys = nullptr;
+    L->g_sort_pl = nullptr;
+  }
+  if (host_io) {
+    const size_t hw = (size_t)L->H * L->W;
+    L->d_cls = c.take<float>((size_t)L->B * L->A * hw);  // foreground half only
+    L->d_box = c.take<float>((size_t)L->B * 4 * L->A * hw);
+    L->d_info = c.take<float>((size_t)L->B * 3);
+    const size_t rows = (size_t)L->B * L->out_rows;
+    size_t o = 0;
+    o += align_up(rows * 5 * sizeof(float), 256);
+    L->off_scores = o;
+    o += align_up(rows * sizeof(float), 256);
+    L->off_keep = o;
+    o += align_up(rows * sizeof(int), 256);
+    L->off_anchor = o;
+    o += align_up(rows * sizeof(int), 256);
+    L->off_nkeep = o;
+    o += align_up((size_t)L->B * 2 * sizeof(int), 256);
+    L->out_bytes = o;
+    L->d_out = c.take<char>(o);
+  }
+  L->total = align_up(c.off, 256);
+  return MXR_OK;
+}
+
+int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layout& L, const float* cls_prob,
+            size_t cls_img_stride, size_t cls_fg_offset, const float* bbox_pred, const float* im_info,
+            const double* anchors, float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor,
+            int32_t* out_nkeep) {
+  AnchorTable at;
+  memset(&at, 0, sizeof(at));
+  memcpy(at.a, anchors, sizeof(double) * 4 * L.A);
+  ProposalGeom pg;
+  pg.g.A = L.A;
+  pg.g.H = L.H;
+  pg.g.W = L.W;
+  pg.g.hc = L.hc;
+  pg.g.wc = L.wc;
+  pg.g.fs = p->feat_stride;
+  pg.n_crop = L.n_crop;
+  pg.n_full = L.n_full;
+  pg.cropped = L.cropped;
+  pg.cls_img_stride = cls_img_stride;
+  pg.cls_fg_offset = cls_fg_offset;
+  h->last_launches = 0;
+  MXR_CUDA(cudaMemsetAsync(L.ctrl, 0, L.zero_bytes, s));
+  const int n_threads = L.n_crop > L.n_full ? L.n_crop : L.n_full;
+  dim3 g1((n_threads + 255) / 256, L.B);
+  prof_begin(h, s, ST_DECODE);
+  decode_filter_kernel<<<g1, 256, 0, s>>>(pg, at, cls_prob, bbox_pred, im_info, p->min_size, L.keys, L.ctrl);
+  prof_end(h, s);
+  TopkArrays ta;
+  ta.keys = L.keys;
+  ta.box = L.box;
+  ta.area = L.area;
+  ta.score = L.score;
+  ta.orig = L.orig;
+  ta.cap = L.cap;
+  ta.g_sort_keys = L.g_sort_keys;
+  ta.g_sort_pl = L.g_sort_pl;
+  ta.g_sort_cap = L.n_pow2_max;
+  size_t smem = 32 * 256 * sizeof(u32);
+  if (L.use_smem_sort) {
+    const size_t pl = (size_t)L.n_pow2_max * 4;
+    smem = (size_t)L.n_pow2_max * 8 + (pl > smem ? pl : smem);
+  }
+  MXR_CUDA(cudaFuncSetAttribute(topk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  prof_begin(h, s, ST_TOPK);
+  topk_sort_kernel<<<L.B, 1024, smem, s>>>(pg, at, ta, cls_prob, bbox_pred, im_info, p->pre_nms_top_n, L.n_pow2_max,
+                                            L.use_smem_sort, L.ctrl);
+  prof_end(h, s);
+  NmsArrays<double> na;
+  na.box = L.box;
+  na.area = L.area;
+  na.score = L.score;
+  na.orig = L.orig;
+  na.cap = L.cap;
+  na.M = L.M;
+  na.m_pitch = L.plan.max_width / 64;
+  na.m_stride = (size_t)L.plan.max_width * na.m_pitch;
+  na.R = L.R;
+  na.r_words = L.cap / 64;
+  na.kept_slot = L.kept_slot;
+  na.keep_cap = L.keep_cap;
+  NmsOutputs o;
+  o.rois = out_rois;
+  o.scores = out_scores;
+  o.keep_pos = out_keep;
+  o.keep_orig = out_anchor;
+  o.nkeep = out_nkeep;
+  o.rows = L.out_rows;
+  o.row_offsets = nullptr;
+  MXR_TRY(run_nms_stripes<double>(h, s, L.ctrl, na, o, L.B, L.n_max, p->post_nms_top_n > 0 ? L.keep_cap : 0, L.plan,
+                                  p->nms_thresh));
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+__global__ void pad_rows_kernel(float* rois, float* scores, int row0, int nkeep, const int* __restrict__ src, int n_pad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_pad) return;
+  const int sidx = src[t];
+  if (sidx < 0 || sidx >= nkeep) return;
+  for (int k = 0; k < 5; ++k) rois[(size_t)(row0 + nkeep + t) * 5 + k] = rois[(size_t)(row0 + sidx) * 5 + k];
+  if (scores) scores[row0 + nkeep + t] = scores[row0 + sidx];
+}
+
+}  // namespace
+
+extern "C" {
+
+int mxr_reserve_proposal(mxr_handle_t hh, const mxr_proposal_params* p) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_reserve_proposal: NULL handle");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  Layout L;
+  MXR_TRY(make_layout(p, p->post_nms_top_n > 0 ? p->post_nms_top_n : p->num_anchors * p->height * p->width, true,
+                      nullptr, &L));
+  MXR_TRY(ensure_device_ws(h, L.total));
+  MXR_TRY(ensure_pinned_ws(h, L.out_bytes));
+  return MXR_OK;
+}
+
+int mxr_proposal_forward(mxr_handle_t hh, void* stream, const mxr_proposal_params* p, const float* cls_prob,
+                         const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
+                         float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
+                         int32_t* out_nkeep) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_forward: NULL handle");
+  MXR_REQUIRE(cls_prob && bbox_pred && im_info && anchors && out_rois && out_nkeep, MXR_ERR_INVALID,
+              "mxr_proposal_forward: NULL array argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  Layout L;
+  MXR_TRY(make_layout(p, out_capacity, false, nullptr, &L));
+  MXR_TRY(ensure_device_ws(h, L.total));
+  MXR_TRY(make_layout(p, out_capacity, false, h->d_ws, &L));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  const size_t hw = (size_t)L.H * L.W;
+  return enqueue(h, s, p, L, cls_prob, 2 * L.A * hw, L.A * hw, bbox_pred, im_info, anchors, out_rois, out_scores,
+                 out_keep, out_anchor_index, out_nkeep);
+}
+
+int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, const float* cls_prob,
+                              const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
+                              float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
+                              int32_t* out_nkeep) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_forward_host: NULL handle");
+  MXR_REQUIRE(cls_prob && bbox_pred && im_info && anchors && out_rois && out_nkeep, MXR_ERR_INVALID,
+              "mxr_proposal_forward_host: NULL array argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  Layout L;
+  MXR_TRY(make_layout(p, out_capacity, true, nullptr, &L));
+  MXR_TRY(ensure_device_ws(h, L.total));
+  MXR_TRY(ensure_pinned_ws(h, L.out_bytes));
+  MXR_TRY(make_layout(p, out_capacity, true, h->d_ws, &L));
+  cudaStream_t s = h->stream;
+  const size_t hw = (size_t)L.H * L.W;
+  // only the foreground half of cls_prob crosses the bus (proposal.py:57)
+  const size_t fg_bytes = (size_t)L.A * hw * sizeof(float);
+  MXR_CUDA(cudaMemcpy2DAsync(L.d_cls, fg_bytes, cls_prob + (size_t)L.A * hw, 2 * fg_bytes, fg_bytes, L.B,
+                             cudaMemcpyHostToDevice, s));
+  MXR_CUDA(cudaMemcpyAsync(L.d_box, bbox_pred, (size_t)L.B * 4 * fg_bytes, cudaMemcpyHostToDevice, s));
+  MXR_CUDA(cudaMemcpyAsync(L.d_info, im_info, (size_t)L.B * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
+  float* d_rois = reinterpret_cast<float*>(L.d_out);
+  float* d_scores = reinterpret_cast<float*>(L.d_out + L.off_scores);
+  int* d_keep = reinterpret_cast<int*>(L.d_out + L.off_keep);
+  int* d_anchor = reinterpret_cast<int*>(L.d_out + L.off_anchor);
+  int* d_nkeep = reinterpret_cast<int*>(L.d_out + L.off_nkeep);
+  MXR_TRY(enqueue(h, s, p, L, L.d_cls, (size_t)L.A * hw, 0, L.d_box, L.d_info, anchors, d_rois, d_scores, d_keep,
+                  d_anchor, d_nkeep));
+  MXR_CUDA(cudaMemcpyAsync(h->h_pin, L.d_out, L.out_bytes, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaStreamSynchronize(s));
+  const size_t rows = (size_t)L.B * L.out_rows;
+  memcpy(out_rois, h->h_pin, rows * 5 * sizeof(float));
+  if (out_scores) memcpy(out_scores, h->h_pin + L.off_scores, rows * sizeof(float));
+  if (out_keep) memcpy(out_keep, h->h_pin + L.off_keep, rows * sizeof(int));
+  if (out_anchor_index) memcpy(out_anchor_index, h->h_pin + L.off_anchor, rows * sizeof(int));
+  memcpy(out_nkeep, h->h_pin + L.off_nkeep, (size_t)L.B * 2 * sizeof(int));
+  for (int b = 0; b < L.B; ++b) {
+    if (out_nkeep[b * 2 + 1] & 1) {
+      set_error("there is nan in input scores or bbox_deltas (image %d)", b);
+      return MXR_ERR_NAN;
+    }
+  }
+  return MXR_OK;
+}
+
+int mxr_proposal_pad(mxr_handle_t hh, void* stream, int image, int rows_per_image, int nkeep, const int32_t* pad_rows,
+                     int n_pad, float* out_rois, float* out_scores) {
+  MXR_REQUIRE(hh != nullptr && out_rois != nullptr, MXR_ERR_INVALID, "mxr_proposal_pad: NULL argument");
+  if (n_pad <= 0) return MXR_OK;
+  MXR_REQUIRE(nkeep > 0, MXR_ERR_EMPTY, "mxr_proposal_pad: nothing kept, cannot pad (proposal.py:136-138)");
+  MXR_REQUIRE(pad_rows != nullptr && nkeep + n_pad <= rows_per_image && image >= 0, MXR_ERR_INVALID,
+              "mxr_proposal_pad: bad pad request nkeep=%d n_pad=%d rows=%d", nkeep, n_pad, rows_per_image);
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  // the draws ride in the pinned staging block; the copy is ordered on the stream
+  MXR_TRY(ensure_pinned_ws(h, (size_t)n_pad * sizeof(int)));
+  MXR_TRY(ensure_device_ws(h, (size_t)n_pad * sizeof(int) + 256));
+  MXR_CUDA(cudaStreamSynchronize(s));  // staging block may still be in use by an earlier call
+  memcpy(h->h_pin, pad_rows, (size_t)n_pad * sizeof(int));
+  int* d_src = reinterpret_cast<int*>(h->d_ws);
+  MXR_CUDA(cudaMemcpyAsync(d_src, h->h_pin, (size_t)n_pad * sizeof(int), cudaMemcpyHostToDevice, s));
+  pad_rows_kernel<<<(n_pad + 127) / 128, 128, 0, s>>>(out_rois, out_scores, image * rows_per_image, nkeep, d_src, n_pad);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,50 @@
+"""helper/processing/nms.py of the reference: ``nms(dets, thresh)`` -> python list of kept rows."""
+import ctypes
+
+import numpy as np
+
+from ... import _lib
+
+
+def nms(dets, thresh, max_keep=0, handle=None):
+    """Greedy NMS (reference: helper/processing/nms.py:4-38).
+
+    dets: (n,5) [x1,y1,x2,y2,score], numpy float32/float64 (arithmetic in that dtype, like
+    numpy) or a device array of those dtypes.  Returns a python list of int row indices in
+    keep order (quirk Q6).  Score ties are processed higher-index-first
+    (``argsort(kind='stable')[::-1]``); the reference leaves tie order to numpy's unstable sort.
+    ``max_keep`` > 0 (extension) stops after that many boxes.
+    """
+    lib = _lib.load()
+    h = handle or _lib.default_handle()
+    if _lib.is_device_array(dets):
+        v = _lib.device_view(dets)
+        if v.dtype not in (np.float32, np.float64) or len(v.shape) != 2 or v.shape[1] != 5:
+            raise ValueError("dets must be (n,5) float32/float64")
+        n = v.shape[0]
+        if n == 0:
+            return []
+        import torch
+        keep = torch.empty((n,), dtype=torch.int32, device=dets.device)
+        nk = torch.empty((2,), dtype=torch.int32, device=dets.device)
+        stream = _lib.current_stream_ptr(dets)
+        _lib.check(lib.mxr_nms(h.ptr, stream, v.ptr, n, 1 if v.dtype == np.float64 else 0, float(thresh),
+                               int(max_keep), keep.data_ptr(), nk.data_ptr()))
+        nk_h = nk.cpu()
+        if int(nk_h[1]) & 1:
+            raise ValueError("nms: NaN in dets")
+        return [int(i) for i in keep[:int(nk_h[0])].cpu().numpy()]
+    dets = np.asarray(dets)
+    if dets.ndim != 2 or dets.shape[1] < 5:
+        raise ValueError("dets must be (n,5)")
+    if dets.dtype != np.float32:
+        dets = dets.astype(np.float64, copy=False)
+    d = np.ascontiguousarray(dets[:, :5])
+    n = d.shape[0]
+    if n == 0:
+        return []
+    keep = np.empty((n,), dtype=np.int32)
+    nk = np.zeros((2,), dtype=np.int32)
+    _lib.check(lib.mxr_nms_host(h.ptr, _lib.hptr(d), n, 1 if d.dtype == np.float64 else 0, float(thresh),
+                                int(max_keep), _lib.hptr(keep), _lib.hptr(nk)))
+    return [int(i) for i in keep[:int(nk[0])]]

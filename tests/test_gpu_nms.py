@@ -1,0 +1,76 @@
+"""GPU parity: nms(dets, thresh) through the C ABI -- keep lists must be bit-exact."""
+import numpy as np
+import pytest
+
+from oracle import restate, synth
+from tests.util import golden
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_nms(dets, thresh, **kw):
+    from mxrcnn_b200.helper.processing.nms import nms
+    return nms(dets, thresh, **kw)
+
+
+def test_nms_vs_reference_fixture():
+    h = golden("helpers")
+    for i in range(6):
+        seed, n, size, th = h["nms%d_spec" % i]
+        dets = synth.class_dets(int(seed), n=int(n), dtype=np.float64 if size == 8 else np.float32)
+        keep = gpu_nms(dets, float(th))
+        assert isinstance(keep, list) and all(isinstance(k, int) for k in keep)
+        assert np.array_equal(np.asarray(keep, dtype=np.int64), h["nms%d_keep" % i]), i
+    assert gpu_nms(np.zeros((0, 5)), 0.3) == []
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,thresh", [(1, 0.5), (63, 0.3), (64, 0.3), (65, 0.7), (1000, 0.5), (5000, 0.3), (9000, 0.7)])
+def test_nms_vs_oracle(dtype, n, thresh):
+    dets = synth.class_dets(n * 7 + 1, n=n, dtype=dtype, clusters=max(2, n // 40))
+    assert gpu_nms(dets, thresh) == [int(i) for i in restate.nms(dets, thresh)]
+
+
+def test_nms_stage_level_on_oracle_dets():
+    """Stage-level parity (unconditional): the oracle's own f64 (n,5) dets of the proposal op
+    (rcnn/rpn/proposal.py:131) fed to the CUDA NMS give the oracle's keep list, all 6000 boxes."""
+    cfg = synth.CONFIGS["voc_test"]
+    cls, box, info = synth.proposal_inputs(3, H=cfg["H"], W=cfg["W"], A=9, im_info=cfg["im_info"])
+    st = restate.proposal_stages(cls, box, info, 16, cfg["scales"], cfg["ratios"], False, cfg["pre"], 0, cfg["thresh"],
+                                 cfg["min_size"])
+    assert st["dets"].dtype == np.float64 and st["dets"].shape == (6000, 5)
+    keep = gpu_nms(st["dets"], cfg["thresh"])
+    assert keep == [int(i) for i in st["keep"]]
+    assert gpu_nms(st["dets"], cfg["thresh"], max_keep=300) == keep[:300]
+
+
+def test_nms_ties_and_degenerate_boxes():
+    rs = np.random.RandomState(5)
+    dets = synth.class_dets(9, n=500)
+    dets[:, 4] = np.round(dets[:, 4] * 10) / 10          # many equal scores
+    assert gpu_nms(dets, 0.4) == [int(i) for i in restate.nms(dets, 0.4)]
+    d32 = dets.astype(np.float32)
+    assert gpu_nms(d32, 0.4) == [int(i) for i in restate.nms(d32, 0.4)]
+    same = np.tile(np.array([[10., 10., 50., 50., 0.5]]), (130, 1))   # identical boxes: only one survives
+    assert gpu_nms(same, 0.5) == [int(i) for i in restate.nms(same, 0.5)] == [129]
+    # zero-area / inverted boxes follow the arithmetic, whatever it gives
+    weird = np.array([[5, 5, 5, 5, .9], [5, 5, 4, 4, .8], [0, 0, 100, 100, .7], [5, 5, 5, 5, .6], [50, 50, 40, 60, .5]],
+                     dtype=np.float64)
+    for th in (0.0, 0.3, 1.0):
+        assert gpu_nms(weird, th) == [int(i) for i in restate.nms(weird, th)]
+    # negative scores and -0.0/+0.0 compare like numpy
+    dets = synth.class_dets(12, n=200)
+    dets[:, 4] = rs.permutation(200) - 100.0
+    dets[7, 4], dets[9, 4] = 0.0, -0.0
+    assert gpu_nms(dets, 0.5) == [int(i) for i in restate.nms(dets, 0.5)]
+
+
+def test_nms_device_array_and_nan():
+    import torch
+    dets = synth.class_dets(77, n=700)
+    t = torch.from_numpy(dets).cuda()
+    assert gpu_nms(t, 0.3) == [int(i) for i in restate.nms(dets, 0.3)]
+    bad = dets.copy()
+    bad[3, 1] = np.nan
+    with pytest.raises(ValueError):
+        gpu_nms(bad, 0.3)

@@ -1,0 +1,155 @@
+"""GPU parity: the CUDA proposal operator (through the C ABI) against the fixtures produced by
+the real reference and against oracle/restate.py on the same seeded inputs."""
+import numpy as np
+import pytest
+
+from oracle import restate, synth
+from tests.util import golden, golden_names, proposal_case
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5  # decoded boxes: exp() is evaluated by CUDA's expf, numpy's differs in the last ulp
+
+
+def run(cls, box, info, cfg, train=False, **kw):
+    from mxrcnn_b200.helper.processing.generate_anchor import generate_anchors
+    from mxrcnn_b200.rcnn.rpn.proposal import proposal_forward
+    anchors = generate_anchors(float(cfg["feat_stride"]), list(cfg["ratios"]), np.array(cfg["scales"], dtype=float))
+    return proposal_forward(cls, box, info, anchors, cfg["feat_stride"], cfg["pre"], cfg["post"], cfg["thresh"],
+                            cfg["min_size"], train_crop=train, want_indices=True, **kw)
+
+
+def check_against(st, out, post):
+    n = int(out["nkeep"][0])
+    assert n == st["nkeep"]
+    assert np.array_equal(out["keep"][0, :n], st["keep"][:n])
+    assert np.array_equal(out["anchor_index"][0, :n], st["keep_anchor_index"][:n])
+    assert np.array_equal(out["scores"][:n], st["scores"][:n])          # scores are gathered: bit-exact
+    np.testing.assert_allclose(out["rois"][:n], st["rois"][:n], rtol=RTOL, atol=1e-4)
+    assert np.all(out["rois"][:, 0] == 0)
+
+
+@pytest.mark.parametrize("name", golden_names("proposal_tiny") + golden_names("proposal_voc_test")
+                         + golden_names("proposal_voc_alt") + golden_names("proposal_wider"))
+def test_proposal_vs_reference_fixture(name):
+    g = golden(name)
+    cls, box, info, cfg, train = proposal_case(g)
+    out = run(cls, box, info, cfg, train, rng=np.random.RandomState(int(g["seed"])))
+    post = cfg["post"]
+    assert out["rois"].shape == (post, 5) and out["rois"].dtype == np.float32
+    assert out["scores"].shape == (post, 1)
+    n = int(g["nkeep"])
+    assert int(out["nkeep"][0]) == n
+    assert np.array_equal(out["keep"][0, :n], g["keep"][:n])
+    assert np.array_equal(out["anchor_index"][0, :n], g["keep_anchor_index"][:n])
+    # full outputs incl. the rows padded from the RNG (same draws: same seed, same call order)
+    assert np.array_equal(out["scores"], g["scores"])
+    np.testing.assert_allclose(out["rois"], g["rois"], rtol=RTOL, atol=1e-4)
+
+
+@pytest.mark.parametrize("seed", [7, 8])
+def test_proposal_padding_draws(seed):
+    g = golden("proposal_pad_s%d" % seed)
+    cfg = dict(synth.CONFIGS["tiny"], post=int(g["post"]), thresh=float(g["thresh"]))
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=9, im_info=cfg["im_info"])
+    out = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
+    assert int(out["nkeep"][0]) == int(g["nkeep"]) < cfg["post"]
+    assert np.array_equal(out["scores"], g["scores"])
+    np.testing.assert_allclose(out["rois"], g["rois"], rtol=RTOL, atol=1e-4)
+
+
+@pytest.mark.parametrize("cfgname,seed", [("tiny", 11), ("tiny", 12), ("voc_test", 13), ("voc_train", 14)])
+def test_proposal_vs_oracle(cfgname, seed):
+    cfg = synth.CONFIGS[cfgname]
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    st = restate.proposal_stages(cls, box, info, cfg["feat_stride"], cfg["scales"], cfg["ratios"], False, cfg["pre"],
+                                 cfg["post"], cfg["thresh"], cfg["min_size"], rng=np.random.RandomState(seed))
+    out = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
+    check_against(st, out, cfg["post"])
+
+
+def test_proposal_score_ties_follow_documented_rule():
+    # equal scores: descending score, then descending row index (argsort(kind='stable')[::-1]);
+    # the reference's default-kind argsort leaves this order undefined
+    cfg = synth.CONFIGS["tiny"]
+    cls, box, info = synth.proposal_inputs(21, H=cfg["H"], W=cfg["W"], A=9, im_info=cfg["im_info"])
+    q = np.round(cls[0, 9:] * 12) / 12.0          # 13 distinct values over 486 anchors
+    cls[0, 9:] = q.astype(np.float32)
+    st = restate.proposal_stages(cls, box, info, 16, cfg["scales"], cfg["ratios"], False, 150, cfg["post"], 0.7, 16)
+    out = run(cls, box, info, dict(cfg, pre=150))
+    check_against(st, out, cfg["post"])
+
+
+def test_proposal_nan_raises_value_error():
+    cfg = synth.CONFIGS["tiny"]
+    cls, box, info = synth.proposal_inputs(0, H=cfg["H"], W=cfg["W"], A=9, im_info=cfg["im_info"])
+    bad = cls.copy()
+    bad[0, 12, 2, 3] = np.nan
+    with pytest.raises(ValueError):
+        run(bad, box, info, cfg)
+    bad = box.copy()
+    bad[0, 5, 1, 1] = np.nan
+    with pytest.raises(ValueError):
+        run(cls, bad, info, cfg)
+    ok = cls.copy()
+    ok[0, 0, 0, 0] = np.nan  # background half is never read (proposal.py:57)
+    run(ok, box, info, cfg)
+
+
+def test_proposal_operator_dropin_numpy():
+    """The reference's own calling convention: Prop built from string kwargs, forward(in_data, out_data)."""
+    from mxrcnn_b200 import operator as mxop
+    from mxrcnn_b200.config import config
+    import mxrcnn_b200.rcnn.rpn.proposal  # noqa: F401  (registers 'proposal')
+    g = golden("proposal_voc_test_s0")
+    cls, box, info, cfg, _ = proposal_case(g)
+    config.TEST.RPN_PRE_NMS_TOP_N, config.TEST.RPN_POST_NMS_TOP_N = cfg["pre"], cfg["post"]
+    prop, op = mxop.create("proposal", feat_stride=16, scales=(8, 16, 32), ratios=(0.5, 1, 2), output_score=True)
+    assert prop.list_arguments() == ["cls_prob", "bbox_pred", "im_info"]
+    assert prop.list_outputs() == ["output", "score"]
+    in_shapes, out_shapes = prop.infer_shape([cls.shape, box.shape, info.shape])
+    assert out_shapes == [(300, 5), (300, 1)]
+    with pytest.raises(ValueError):
+        prop.infer_shape([(2,) + cls.shape[1:], (2,) + box.shape[1:], (2, 3)])
+    outs = [np.zeros(s, np.float32) for s in out_shapes]
+    op.forward(False, ["write", "write"], [cls, box, info], outs, [])
+    assert np.array_equal(outs[1], g["scores"])
+    np.testing.assert_allclose(outs[0], g["rois"], rtol=RTOL, atol=1e-4)
+    grads = [np.ones_like(cls), np.ones_like(box)]
+    op.backward(["write", "write"], [], [cls, box, info], outs, grads, [])
+    assert not grads[0].any() and not grads[1].any()
+
+
+def test_proposal_device_arrays_and_batch():
+    """Device-pointer entry point (torch tensors via data_ptr/DLPack), batch of 8 = C2; every image
+    must equal its own single-image host-path result."""
+    import torch
+    cfg = synth.CONFIGS["voc_test"]
+    seeds = list(range(30, 38))
+    cls, box, info = synth.proposal_batch(seeds, cfg)
+    dev = torch.device("cuda:0")
+    out = run(torch.from_numpy(cls).to(dev), torch.from_numpy(box).to(dev), torch.from_numpy(info).to(dev), cfg)
+    rois = out["rois"].cpu().numpy().reshape(8, cfg["post"], 5)
+    scores = out["scores"].cpu().numpy().reshape(8, cfg["post"])
+    keep = out["keep"].cpu().numpy()
+    for i, s in enumerate(seeds):
+        one = run(cls[i:i + 1], box[i:i + 1], info[i:i + 1], cfg)
+        assert np.array_equal(one["keep"][0], keep[i])
+        assert np.array_equal(one["scores"][:, 0], scores[i])
+        assert np.array_equal(one["rois"][:, 1:], rois[i][:, 1:])
+        assert np.all(rois[i][:, 0] == i)
+        if i < 2:
+            st = restate.proposal_stages(cls[i:i + 1], box[i:i + 1], info[i:i + 1], 16, cfg["scales"], cfg["ratios"],
+                                         False, cfg["pre"], cfg["post"], cfg["thresh"], cfg["min_size"],
+                                         nms_stop_after=cfg["post"])
+            assert np.array_equal(st["keep"], keep[i])
+
+
+def test_proposal_first_stripe_width_does_not_change_results():
+    cfg = synth.CONFIGS["voc_test"]
+    cls, box, info = synth.proposal_inputs(40, H=cfg["H"], W=cfg["W"], A=9, im_info=cfg["im_info"])
+    base = run(cls, box, info, cfg)
+    for fs in (64, 256, 4096):
+        o = run(cls, box, info, cfg, first_stripe=fs)
+        assert np.array_equal(o["keep"], base["keep"]) and np.array_equal(o["rois"], base["rois"])
