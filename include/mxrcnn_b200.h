@@ -15,7 +15,7 @@
  *     host pointers.  The caller owns every in/out buffer.  The library owns only the
  *     handle's workspace (device scratch + pinned staging), which grows on demand in
  *     mxr_reserve_*() -- call those at set-up to keep allocations out of the hot call.
- *   - `stream` is a cudaStream_t passed as void* (NULL = the handle's own stream).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = CUDA's legacy default stream, as everywhere in CUDA).
  *     Device-pointer calls only enqueue work and never synchronise.  *_host calls
  *     copy in, compute, copy out and return after the results are in the host buffers.
  *   - a handle is bound to one device and is not thread-safe; use one per thread/stream.
@@ -57,7 +57,7 @@ int mxr_create(int device, mxr_handle_t* out);
 int mxr_destroy(mxr_handle_t h);
 /* Bytes of device workspace currently held by the handle. */
 size_t mxr_workspace_bytes(mxr_handle_t h);
-/* Wait for everything enqueued on `stream` (NULL = handle stream). */
+/* Wait for everything enqueued on `stream`. */
 int mxr_synchronize(mxr_handle_t h, void* stream);
 
 /* Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg;

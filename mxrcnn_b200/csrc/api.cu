@@ -146,7 +146,7 @@ int mxr_last_launch_count(mxr_handle_t hh) { return hh ? reinterpret_cast<Handle
 int mxr_synchronize(mxr_handle_t hh, void* stream) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_synchronize: NULL handle");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaStreamSynchronize(stream ? (cudaStream_t)stream : h->stream));
+  MXR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   return MXR_OK;
 }
 

@@ -87,6 +87,7 @@ struct Handle {
   ProfRec* prof;
   int prof_cap, prof_used;
   int last_launches;  // kernels launched by the most recent call
+  int smem_attr[4];   // largest dynamic-smem opt-in already set per kernel (0 topk, 1 prep f32, 2 prep f64)
 };
 
 // Bracket one kernel launch.  No-ops unless mxr_profile_enable(h, 1) was called.

@@ -148,7 +148,11 @@ int enqueue_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets, doub
   pa.g_sort_pl = L.g_sort_pl;
   pa.g_sort_cap = L.n_pow2_max;
   size_t smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 12 : 16;
-  MXR_CUDA(cudaFuncSetAttribute(nms_prepare_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int slot = sizeof(T) == 8 ? 2 : 1;
+  if ((int)smem > h->smem_attr[slot]) {
+    MXR_CUDA(cudaFuncSetAttribute(nms_prepare_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    h->smem_attr[slot] = (int)smem;
+  }
   prof_begin(h, s, ST_NMS_PREP);
   nms_prepare_kernel<T><<<L.P, 1024, smem, s>>>(dets, L.offsets, pa, L.n_pow2_max, L.use_smem_sort, L.ctrl);
   prof_end(h, s);
@@ -248,7 +252,7 @@ int mxr_nms(mxr_handle_t hh, void* stream, const void* dets, int n, int dtype, d
   Handle* h = reinterpret_cast<Handle*>(hh);
   MXR_CUDA(cudaSetDevice(h->device));
   const int32_t offs[2] = {0, n};
-  return run(h, stream ? (cudaStream_t)stream : h->stream, dets, false, offs, 1, dtype, thresh, max_keep, keep_out,
+  return run(h, (cudaStream_t)stream, dets, false, offs, 1, dtype, thresh, max_keep, keep_out,
              nkeep_out);
 }
 
@@ -267,7 +271,7 @@ int mxr_nms_batched(mxr_handle_t hh, void* stream, const void* dets, const int32
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms_batched: NULL handle");
   Handle* h = reinterpret_cast<Handle*>(hh);
   MXR_CUDA(cudaSetDevice(h->device));
-  return run(h, stream ? (cudaStream_t)stream : h->stream, dets, false, offsets, n_problems, dtype, thresh, max_keep,
+  return run(h, (cudaStream_t)stream, dets, false, offsets, n_problems, dtype, thresh, max_keep,
              keep_out, nkeep_out);
 }
 

@@ -146,7 +146,10 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     const size_t pl = (size_t)L.n_pow2_max * 4;
     smem = (size_t)L.n_pow2_max * 8 + (pl > smem ? pl : smem);
   }
-  MXR_CUDA(cudaFuncSetAttribute(topk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if ((int)smem > h->smem_attr[0]) {
+    MXR_CUDA(cudaFuncSetAttribute(topk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    h->smem_attr[0] = (int)smem;
+  }
   prof_begin(h, s, ST_TOPK);
   topk_sort_kernel<<<L.B, 1024, smem, s>>>(pg, at, ta, cls_prob, bbox_pred, im_info, p->pre_nms_top_n, L.n_pow2_max,
                                             L.use_smem_sort, L.ctrl);
@@ -216,7 +219,7 @@ int mxr_proposal_forward(mxr_handle_t hh, void* stream, const mxr_proposal_param
   MXR_TRY(make_layout(p, out_capacity, false, nullptr, &L));
   MXR_TRY(ensure_device_ws(h, L.total));
   MXR_TRY(make_layout(p, out_capacity, false, h->d_ws, &L));
-  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  cudaStream_t s = (cudaStream_t)stream;
   const size_t hw = (size_t)L.H * L.W;
   return enqueue(h, s, p, L, cls_prob, 2 * L.A * hw, L.A * hw, bbox_pred, im_info, anchors, out_rois, out_scores,
                  out_keep, out_anchor_index, out_nkeep);
@@ -277,7 +280,7 @@ int mxr_proposal_pad(mxr_handle_t hh, void* stream, int image, int rows_per_imag
               "mxr_proposal_pad: bad pad request nkeep=%d n_pad=%d rows=%d", nkeep, n_pad, rows_per_image);
   Handle* h = reinterpret_cast<Handle*>(hh);
   MXR_CUDA(cudaSetDevice(h->device));
-  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  cudaStream_t s = (cudaStream_t)stream;
   // the draws ride in the pinned staging block; the copy is ordered on the stream
   MXR_TRY(ensure_pinned_ws(h, (size_t)n_pad * sizeof(int)));
   MXR_TRY(ensure_device_ws(h, (size_t)n_pad * sizeof(int) + 256));
