@@ -138,6 +138,22 @@ int mxr_nms_host(mxr_handle_t h, const void* dets, int n, int dtype, double thre
 int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_t* offsets, int n_problems, int dtype,
                     double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out);
 
+/* ---- nms without any allocation (no counterpart in the reference) --------------------- */
+/* Same result as mxr_nms on device arrays, for callers that cannot allocate GPU memory: a plug-in
+ * inside a framework whose pool already owns the whole device (a cudaMalloc of ours would fail or
+ * eat into that pool), or a request path that cannot take the device-wide stall of cudaMalloc /
+ * cudaFree.  Takes no handle and allocates nothing: the scratch is a fixed 640 KiB array inside the
+ * library image, held by every GPU that loads the library until the process exits.
+ *   - n <= MXR_NMS_NOALLOC_MAX_BOXES, otherwise MXR_ERR_LIMIT (use mxr_nms for larger inputs).
+ *   - runs on the CURRENT device; the first call on a device resolves the array's device address
+ *     (one-time set-up): make that call before any stream capture starts.
+ *   - every call on a device reuses the same array (it is cleared where needed at the start of each
+ *     call), so two calls whose GPU work overlaps race: keep them on one stream or serialise them.
+ * dets / keep_out / nkeep_out are device pointers as for mxr_nms; nothing is synchronised. */
+#define MXR_NMS_NOALLOC_MAX_BOXES 2048
+int mxr_nms_noalloc(void* stream, const void* dets, int n, int dtype, double thresh, int max_keep, int32_t* keep_out,
+                    int32_t* nkeep_out);
+
 #ifdef __cplusplus
 }
 #endif

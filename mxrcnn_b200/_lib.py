@@ -59,6 +59,7 @@ SIGNATURES = {
     "mxr_nms_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
     "mxr_nms_batched": (ctypes.c_int, [_VP, _VP, _VP, c_int_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                        ctypes.c_int, _VP, _VP]),
+    "mxr_nms_noalloc": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
 }
 
 _lib = None

@@ -276,3 +276,106 @@ int mxr_nms_batched(mxr_handle_t hh, void* stream, const void* dets, const int32
 }
 
 }  // extern "C"
+
+// =========================================================================================
+// mxr_nms_noalloc -- nms(dets, thresh) for callers that must not allocate device memory.
+//
+// Who needs this: a plug-in that runs inside a host framework which has already handed the
+// whole GPU to its own memory pool (a cudaMalloc from the plug-in then fails, or steals from
+// and fragments that pool), and a serving loop that cannot afford cudaMalloc/cudaFree on its
+// request path because both synchronise the whole device and stall every other stream.
+// mxr_nms() keeps its scratch in the handle's workspace, which it obtains with cudaMalloc the
+// first time (and whenever a larger problem arrives).  This variant takes no handle and never
+// calls cudaMalloc, cudaFree, cudaHostAlloc or any other allocating routine: its scratch is
+// the fixed array below, which is part of the library image -- every GPU that loads the
+// library holds these 640 KiB until the process exits.
+//
+// Limits and rules (also in include/mxrcnn_b200.h):
+//   * at most MXR_NMS_NOALLOC_MAX_BOXES (2048) boxes per call; larger n -> MXR_ERR_LIMIT.
+//   * the first call on each device looks up the device address of the array
+//     (cudaGetSymbolAddress, once per device, with that device current).  Make that first
+//     call during set-up, before any stream capture begins.
+//   * all calls on one device share the one array, and it keeps whatever the previous call
+//     left in it.  Each call therefore clears the words that must start at zero (control
+//     block, suppression bit words) in its first kernel.  Two calls whose GPU work overlaps
+//     (different streams, or different host threads) race on the array: serialise them.
+// =========================================================================================
+namespace {
+
+const int kNoAllocMaxBoxes = 2048;
+const size_t kNoAllocBytes = 640 * 1024;
+const int kNoAllocMaxDevices = 64;
+
+// Scratch of mxr_nms_noalloc.  In HOST code this name is only a handle for
+// cudaGetSymbolAddress -- it is not a device address and must never be passed to a kernel.
+static __device__ __align__(256) unsigned char g_nms_noalloc_scratch[kNoAllocBytes];
+
+// Device address of g_nms_noalloc_scratch on each device, filled on first use.
+unsigned char* g_nms_noalloc_addr[kNoAllocMaxDevices];
+
+// First kernel of every call: the array still holds the previous call's data.
+__global__ void nms_noalloc_reset_kernel(unsigned char* zero_from, size_t zero_bytes, int* offsets, int n) {
+  const size_t words = zero_bytes / sizeof(u32);
+  u32* z = reinterpret_cast<u32*>(zero_from);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (size_t)gridDim.x * blockDim.x) z[i] = 0u;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    offsets[0] = 0;
+    offsets[1] = n;
+  }
+}
+
+int nms_noalloc_scratch(unsigned char** out, int* device_out) {
+  int dev = -1;
+  MXR_CUDA(cudaGetDevice(&dev));
+  MXR_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, MXR_ERR_LIMIT, "mxr_nms_noalloc: device index %d not supported", dev);
+  if (g_nms_noalloc_addr[dev] == nullptr) {
+    // once per device, with that device current (it is: we just asked which one is)
+    unsigned char* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_nms_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("mxr_nms_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return MXR_ERR_CUDA;
+    }
+    g_nms_noalloc_addr[dev] = ptr;
+  }
+  *out = g_nms_noalloc_addr[dev];
+  *device_out = dev;
+  return MXR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mxr_nms_noalloc(void* stream, const void* dets, int n, int dtype, double thresh, int max_keep, int32_t* keep_out,
+                    int32_t* nkeep_out) {
+  MXR_REQUIRE(dtype == MXR_DTYPE_F32 || dtype == MXR_DTYPE_F64, MXR_ERR_INVALID, "mxr_nms_noalloc: dtype must be f32 or f64");
+  MXR_REQUIRE(n >= 0 && nkeep_out != nullptr, MXR_ERR_INVALID, "mxr_nms_noalloc: bad n or NULL nkeep_out");
+  MXR_REQUIRE(n == 0 || (dets != nullptr && keep_out != nullptr), MXR_ERR_INVALID, "mxr_nms_noalloc: NULL dets/keep_out");
+  MXR_REQUIRE(n <= kNoAllocMaxBoxes, MXR_ERR_LIMIT,
+              "mxr_nms_noalloc: %d boxes exceed the fixed scratch (maximum %d per call); use mxr_nms", n,
+              kNoAllocMaxBoxes);
+  unsigned char* scratch = nullptr;
+  int dev = 0;
+  MXR_TRY(nms_noalloc_scratch(&scratch, &dev));
+  const size_t esize = dtype == MXR_DTYPE_F64 ? 8 : 4;
+  NmsLayout L;
+  make_layout(1, n, n, max_keep, esize, false, reinterpret_cast<char*>(scratch), &L);
+  MXR_REQUIRE(L.total <= kNoAllocBytes, MXR_ERR_LIMIT, "mxr_nms_noalloc: layout of %zu bytes exceeds the %zu-byte scratch",
+              L.total, kNoAllocBytes);
+  cudaStream_t s = (cudaStream_t)stream;
+  Handle tmp;  // plain host struct for the shared launch helpers: no workspace, profiling off
+  memset(&tmp, 0, sizeof(tmp));
+  tmp.device = dev;
+  tmp.smem_attr[1] = tmp.smem_attr[2] = 1 << 30;  // <= 24 KiB of dynamic smem here: no opt-in needed
+  nms_noalloc_reset_kernel<<<4, 256, 0, s>>>(reinterpret_cast<unsigned char*>(L.ctrl), L.zero_bytes, L.offsets, n);
+  if (dtype == MXR_DTYPE_F64) {
+    MXR_TRY(enqueue_t<double>(&tmp, s, L, reinterpret_cast<const double*>(dets), thresh, max_keep, keep_out, nkeep_out));
+  } else {
+    MXR_TRY(enqueue_t<float>(&tmp, s, L, reinterpret_cast<const float*>(dets), thresh, max_keep, keep_out, nkeep_out));
+  }
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+}  // extern "C"
