@@ -137,7 +137,7 @@ int mxr_profile_read(mxr_handle_t hh, int max_stages, double* total_ms, int32_t*
 const char* mxr_profile_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"memset",          "decode_filter_kernel", "topk_sort_kernel", "nms_stripe_kernel",
                                         "nms_scan_kernel", "nms_prepare_kernel",   "boxes_kernels",    "overlaps_kernels",
-                                        "anchor_target_kernels", "proposal_target_kernels"};
+                                        "anchor_target_kernels", "proposal_target_kernels", "nms_coop_kernel"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 

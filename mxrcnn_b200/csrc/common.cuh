@@ -66,7 +66,8 @@ enum Stage {
   ST_OVERLAPS = 7,
   ST_ANCHOR_TARGET = 8,
   ST_PROPOSAL_TARGET = 9,
-  ST_COUNT = 10
+  ST_NMS_COOP = 10,
+  ST_COUNT = 11
 };
 
 struct ProfRec {
@@ -87,7 +88,8 @@ struct Handle {
   ProfRec* prof;
   int prof_cap, prof_used;
   int last_launches;  // kernels launched by the most recent call
-  int smem_attr[4];   // largest dynamic-smem opt-in already set per kernel (0 topk, 1 prep f32, 2 prep f64)
+  int smem_attr[8];   // largest dynamic-smem opt-in already set per kernel (0 topk, 1 prep f32, 2 prep f64, 3.. coop)
+  int coop_grid[4];   // co-resident grid size of the cooperative kernels (0: not queried yet)
 };
 
 // Bracket one kernel launch.  No-ops unless mxr_profile_enable(h, 1) was called.

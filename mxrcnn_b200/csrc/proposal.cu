@@ -1,6 +1,7 @@
 // rcnn/rpn/proposal.py:39-149 -- host side of the proposal operator.
 #include <string.h>
 
+#include "nms_coop.cuh"
 #include "nms_host.cuh"
 #include "proposal_kernels.cuh"
 
@@ -13,7 +14,7 @@ const int kSmemSortMax = 16384;  // pairs that fit the 227 KB of shared memory (
 struct Layout {
   // derived sizes
   int B, A, H, W, hc, wc, n_crop, n_full, cropped;
-  int n_max, cap, keep_cap, out_rows, n_pow2_max, use_smem_sort;
+  int n_max, cap, keep_cap, out_rows, n_pow2_max, use_smem_sort, head;
   StripePlan plan;
   // device carve
   Ctrl* ctrl;
@@ -27,7 +28,6 @@ struct Layout {
   int* kept_slot;
   u64* M;
   u64* g_sort_keys;
-  u32* g_sort_pl;
   // staging for the *_host entry point
   float* d_cls;
   float* d_box;
@@ -62,6 +62,12 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   L->n_pow2_max = pow2_ceil(L->n_max < 2 ? 2 : L->n_max);
   L->use_smem_sort = L->n_pow2_max <= kSmemSortMax;
   L->plan = plan_stripes(L->n_max, p->post_nms_top_n > 0 ? L->keep_cap : 0, p->first_stripe);
+  // "head": the prefix of the candidate order that is sorted up front (whole 1024-box stripes);
+  // the rest is sorted by the deferred phase of the NMS kernel only if some image gets that far
+  L->head = round_up_int(L->plan.first, kCoopW);
+  if (L->head > kMaxStripe) L->head = kMaxStripe;
+  if (L->head >= L->n_max) L->head = round_up_int(L->n_max, 64);
+  L->plan.max_width = kCoopW;
   Carver c(base);
   const int r_words = L->cap / 64;
   L->ctrl = c.take<Ctrl>(L->B);
@@ -75,13 +81,7 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   L->kept_slot = c.take<int>((size_t)L->B * L->keep_cap);
   const size_t m_words = (size_t)L->plan.max_width * (L->plan.max_width / 64);
   L->M = c.take<u64>((size_t)L->B * m_words);
-  if (!L->use_smem_sort) {
-    L->g_sort_keys = c.take<u64>((size_t)L->B * L->n_pow2_max);
-    L->g_sort_pl = c.take<u32>((size_t)L->B * L->n_pow2_max);
-  } else {
-    L->g_sort_keys = nullptr;
-    L->g_sort_pl = nullptr;
-  }
+  L->g_sort_keys = L->use_smem_sort ? nullptr : c.take<u64>((size_t)L->B * L->n_pow2_max);
   if (host_io) {
     const size_t hw = (size_t)L->H * L->W;
     L->d_cls = c.take<float>((size_t)L->B * L->A * hw);  // foreground half only
@@ -104,6 +104,17 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   L->total = align_up(c.off, 256);
   return MXR_OK;
 }
+
+// Deferred phase of the NMS kernel: full top-k (select + sort + re-decode) of one image.
+struct ProposalTier2 {
+  TopkCall tc;
+  AnchorTable at;
+  int head;
+  __device__ __forceinline__ bool wanted(int) const { return true; }
+  __device__ __forceinline__ void run(int b, Ctrl* ctrl, unsigned char* smem, u32* st, int* cnt) const {
+    topk_body<0>(tc, at, 0, ctrl, b, smem, st, cnt);
+  }
+};
 
 int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layout& L, const float* cls_prob,
             size_t cls_img_stride, size_t cls_fg_offset, const float* bbox_pred, const float* im_info,
@@ -131,52 +142,82 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   prof_begin(h, s, ST_DECODE);
   decode_filter_kernel<<<g1, 256, 0, s>>>(pg, at, cls_prob, bbox_pred, im_info, p->min_size, L.keys, L.ctrl);
   prof_end(h, s);
-  TopkArrays ta;
-  ta.keys = L.keys;
-  ta.box = L.box;
-  ta.area = L.area;
-  ta.score = L.score;
-  ta.orig = L.orig;
-  ta.cap = L.cap;
-  ta.g_sort_keys = L.g_sort_keys;
-  ta.g_sort_pl = L.g_sort_pl;
-  ta.g_sort_cap = L.n_pow2_max;
-  size_t smem = 32 * 256 * sizeof(u32);
-  if (L.use_smem_sort) {
-    const size_t pl = (size_t)L.n_pow2_max * 4;
-    smem = (size_t)L.n_pow2_max * 8 + (pl > smem ? pl : smem);
-  }
-  if ((int)smem > h->smem_attr[0]) {
-    MXR_CUDA(cudaFuncSetAttribute(topk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    h->smem_attr[0] = (int)smem;
-  }
+  TopkCall tc;
+  tc.pg = pg;
+  tc.ta.keys = L.keys;
+  tc.ta.box = L.box;
+  tc.ta.area = L.area;
+  tc.ta.score = L.score;
+  tc.ta.orig = L.orig;
+  tc.ta.cap = L.cap;
+  tc.ta.g_sort_keys = L.g_sort_keys;
+  tc.ta.g_sort_cap = L.n_pow2_max;
+  tc.cls_prob = cls_prob;
+  tc.bbox_pred = bbox_pred;
+  tc.im_info = im_info;
+  tc.pre_nms = p->pre_nms_top_n;
+  // ---- tier 1: sort only the head of the candidate order (<= 4096 boxes: 32 KiB of smem) ----
+  const int head_pow2 = pow2_ceil(L.head < 2 ? 2 : L.head);
+  size_t smem1 = (size_t)head_pow2 * 8;
+  if (smem1 < 32 * 256 * sizeof(u32)) smem1 = 32 * 256 * sizeof(u32);
+  tc.smem_pairs = (int)(smem1 / 8);
   prof_begin(h, s, ST_TOPK);
-  topk_sort_kernel<<<L.B, 1024, smem, s>>>(pg, at, ta, cls_prob, bbox_pred, im_info, p->pre_nms_top_n, L.n_pow2_max,
-                                            L.use_smem_sort, L.ctrl);
+  if (L.n_crop <= 24 * 1024) {
+    topk_kernel<24><<<L.B, 1024, smem1, s>>>(tc, at, L.head, 0, L.ctrl);
+  } else {
+    topk_kernel<0><<<L.B, 1024, smem1, s>>>(tc, at, L.head, 0, L.ctrl);
+  }
   prof_end(h, s);
-  NmsArrays<double> na;
-  na.box = L.box;
-  na.area = L.area;
-  na.score = L.score;
-  na.orig = L.orig;
-  na.cap = L.cap;
-  na.M = L.M;
-  na.m_pitch = L.plan.max_width / 64;
-  na.m_stride = (size_t)L.plan.max_width * na.m_pitch;
-  na.R = L.R;
-  na.r_words = L.cap / 64;
-  na.kept_slot = L.kept_slot;
-  na.keep_cap = L.keep_cap;
-  NmsOutputs o;
-  o.rois = out_rois;
-  o.scores = out_scores;
-  o.keep_pos = out_keep;
-  o.keep_orig = out_anchor;
-  o.nkeep = out_nkeep;
-  o.rows = L.out_rows;
-  o.row_offsets = nullptr;
-  MXR_TRY(run_nms_stripes<double>(h, s, L.ctrl, na, o, L.B, L.n_max, p->post_nms_top_n > 0 ? L.keep_cap : 0, L.plan,
-                                  p->nms_thresh));
+  // ---- NMS: one cooperative kernel; its deferred phase sorts the rest if an image needs it ----
+  CoopArgs<double> ca;
+  ca.ctrl = L.ctrl;
+  ca.a.box = L.box;
+  ca.a.area = L.area;
+  ca.a.score = L.score;
+  ca.a.orig = L.orig;
+  ca.a.cap = L.cap;
+  ca.a.M = L.M;
+  ca.a.m_pitch = kCoopSW;
+  ca.a.m_stride = (size_t)kCoopW * kCoopSW;
+  ca.a.R = L.R;
+  ca.a.r_words = L.cap / 64;
+  ca.a.kept_slot = L.kept_slot;
+  ca.a.keep_cap = L.keep_cap;
+  ca.o.rois = out_rois;
+  ca.o.scores = out_scores;
+  ca.o.keep_pos = out_keep;
+  ca.o.keep_orig = out_anchor;
+  ca.o.nkeep = out_nkeep;
+  ca.o.rows = L.out_rows;
+  ca.o.row_offsets = nullptr;
+  ca.B = L.B;
+  ca.n_max = L.n_max;
+  ca.max_keep = p->post_nms_top_n > 0 ? L.keep_cap : 0;
+  ca.tier2_at = (L.head < L.n_max) ? L.head / kCoopW : -1;
+  ca.thr = p->nms_thresh;
+  ProposalTier2 t2;
+  t2.tc = tc;
+  t2.at = at;
+  t2.head = L.head;
+  size_t tier2_smem = 0;
+  if (ca.tier2_at >= 0) tier2_smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 8 : 32 * 256 * sizeof(u32);
+  const size_t smem2 = coop_smem_bytes(sizeof(double4), sizeof(double), tier2_smem);
+  t2.tc.smem_pairs = L.use_smem_sort ? (int)(smem2 / 8) : 0;
+  if (h->coop_grid[0] == 0 || (int)smem2 > h->smem_attr[3]) {
+    MXR_CUDA(cudaFuncSetAttribute(nms_coop_kernel<double, ProposalTier2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem2));
+    h->smem_attr[3] = (int)smem2;
+    int per_sm = 0, sms = 0;
+    MXR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_coop_kernel<double, ProposalTier2>, 1024, smem2));
+    MXR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+    MXR_REQUIRE(per_sm >= 1, MXR_ERR_CUDA, "proposal: the cooperative NMS kernel does not fit on an SM");
+    h->coop_grid[0] = per_sm * sms;
+  }
+  void* kargs[] = {(void*)&ca, (void*)&t2};
+  prof_begin(h, s, ST_NMS_COOP);
+  MXR_CUDA(cudaLaunchCooperativeKernel((const void*)nms_coop_kernel<double, ProposalTier2>, dim3(h->coop_grid[0]), dim3(1024),
+                                       kargs, smem2, s));
+  prof_end(h, s);
   MXR_CUDA(cudaGetLastError());
   return MXR_OK;
 }

@@ -81,90 +81,98 @@ struct TopkArrays {
   float* score;
   int* orig;            // p index
   int cap;
-  u64* g_sort_keys;     // global fallback for the sort buffers (n_pow2 > smem capacity), [b][n_pow2_cap]
-  u32* g_sort_pl;
+  u64* g_sort_keys;     // global fallback for the sort buffer (n_pow2 > smem capacity), [b][g_sort_cap]
   int g_sort_cap;
 };
 
-// One CTA (1024 threads) per image.  dynamic smem: sort buffers (if they fit) ; the
-// histogram scratch of the select aliases the payload buffer.
-__global__ void __launch_bounds__(1024) topk_sort_kernel(ProposalGeom pg, AnchorTable at, TopkArrays ta,
-                                                         const float* __restrict__ cls_prob,
-                                                         const float* __restrict__ bbox_pred,
-                                                         const float* __restrict__ im_info, int pre_nms, int n_pow2_max,
-                                                         int use_smem_sort, Ctrl* __restrict__ ctrl) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ u32 st[8];
-  __shared__ int s_cnt;
-  const int b = blockIdx.x;
+struct TopkCall {
+  ProposalGeom pg;
+  TopkArrays ta;
+  const float* cls_prob;
+  const float* bbox_pred;
+  const float* im_info;
+  int pre_nms;        // proposal.py:124-125 (<= 0: all)
+  int smem_pairs;     // u64 slots available in shared memory for the sort buffer (0: use the global one)
+};
+
+// Body shared by the stand-alone kernel and the cooperative NMS kernel's deferred ("tier 2") phase.
+// One CTA (blockDim.x threads, all of them) per image:
+//   1. radix-select the threshold of the top-k_sel boxes under (score desc, row index desc)  -- proposal.py:123-125
+//   2. compact them, sort by (score desc, row index ASC)  -- nms.py:19 re-sorts the already
+//      descending list, which reverses runs of equal scores
+//   3. re-decode the selected boxes into processing order.
+// k_limit > 0 selects only the first min(k_limit, k) boxes of the order ("head"): greedy NMS walks the list
+// in order and usually fills its post-NMS quota long before the tail is needed.
+// ITEMS > 0: the image's keys live in registers (ITEMS per thread, n_crop <= ITEMS*blockDim.x).
+// smem: max(8 * n_pow2, 32 KiB) bytes; the select's histograms alias the sort buffer.
+template <int ITEMS>
+__device__ __forceinline__ void topk_body(const TopkCall& tc, const AnchorTable& at, int k_limit, Ctrl* __restrict__ ctrl, int b,
+                                          unsigned char* smem_raw, u32* st, int* s_cnt) {
   const int tid = threadIdx.x;
+  const ProposalGeom& pg = tc.pg;
   const DecodeGeom& g = pg.g;
+  const TopkArrays& ta = tc.ta;
   const int hwc = g.hc * g.wc;
   const u32* keys = ta.keys + (size_t)b * pg.n_crop;
   const int n_valid = ctrl[b].n_valid;
-  const int k = (pre_nms > 0) ? min(pre_nms, n_valid) : n_valid;  // proposal.py:124-125
+  const int k = (tc.pre_nms > 0) ? min(tc.pre_nms, n_valid) : n_valid;  // proposal.py:124-125
+  const int k_sel = (k_limit > 0 && k_limit < k) ? k_limit : k;
   if (tid == 0) {
     ctrl[b].n = k;
-    s_cnt = 0;
+    *s_cnt = 0;
   }
-  if (k == 0) return;
-  const int n_pow2 = max(2, (int)(1u << (32 - __clz(k - 1))));
-  u64* skeys;
-  u32* spl;
-  u32* hist;
-  if (use_smem_sort) {
-    skeys = reinterpret_cast<u64*>(smem_raw);
-    spl = reinterpret_cast<u32*>(smem_raw + (size_t)n_pow2_max * 8);
-    hist = spl;  // select scratch (32 warps * 256 bins) aliases the payload buffer
-  } else {
-    skeys = ta.g_sort_keys + (size_t)b * ta.g_sort_cap;
-    spl = ta.g_sort_pl + (size_t)b * ta.g_sort_cap;
-    hist = reinterpret_cast<u32*>(smem_raw);
+  if (k_sel == 0) return;
+  const int n_pow2 = max(2, (int)(1u << (32 - __clz(k_sel - 1))));
+  u64* skeys = (n_pow2 <= tc.smem_pairs) ? reinterpret_cast<u64*>(smem_raw) : ta.g_sort_keys + (size_t)b * ta.g_sort_cap;
+  u32* hist = reinterpret_cast<u32*>(smem_raw);
+  const int n_iter = (pg.n_crop + blockDim.x - 1) / blockDim.x;
+  u32 rk[ITEMS > 0 ? ITEMS : 1];
+  if (ITEMS > 0) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int q = tid + i * blockDim.x;
+      rk[i] = (q < pg.n_crop) ? __ldg(keys + q) : 0u;
+    }
   }
-  // ---- select: threshold T of the top-k under (score desc, row index desc) -- proposal.py:123 ----
+  auto key_of = [&](int i, int q) -> u32 {
+    if (ITEMS > 0) return rk[i];
+    return (q < pg.n_crop) ? __ldg(keys + q) : 0u;
+  };
   u64 T = 1;  // every valid composite is >= 2^32
-  if (k < n_valid) {
-    T = block_radix_select(pg.n_crop, k, hist, st, [&](int q, u64* c) {
-      const u32 key = keys[q];
+  if (k_sel < n_valid) {
+    T = block_radix_select<ITEMS>(n_iter, k_sel, hist, st, [&](int i, int q, u64* c) {
+      const u32 key = key_of(i, q);
       *c = ((u64)key << 32) | (u32)q_to_p(q, hwc, g.A);
       return key != 0u;
     });
   }
   __syncthreads();
-  // ---- compact the selected set; sort key = (score desc, row index ASC): nms.py:19 re-sorts
-  //      the already descending list, which reverses runs of equal scores ----
-  const int n_round = (pg.n_crop + blockDim.x - 1) / blockDim.x * blockDim.x;
-  for (int q = tid; q < n_round; q += blockDim.x) {
-    bool sel = false;
-    u32 key = 0, p = 0;
-    if (q < pg.n_crop) {
-      key = keys[q];
-      p = (u32)q_to_p(q, hwc, g.A);
-      sel = key != 0u && (((u64)key << 32) | p) >= T;
-    }
+  auto compact = [&](int i, int q) {
+    const u32 key = key_of(i, q);
+    const u32 p = (u32)q_to_p(q, hwc, g.A);
+    const bool sel = key != 0u && (((u64)key << 32) | p) >= T;
     const u32 m = __ballot_sync(0xffffffffu, sel);
     int base = 0;
-    if ((tid & 31) == 0 && m) base = atomicAdd(&s_cnt, __popc(m));
+    if ((tid & 31) == 0 && m) base = atomicAdd(s_cnt, __popc(m));
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (sel) {
-      const int pos = base + __popc(m & ((1u << (tid & 31)) - 1u));
-      skeys[pos] = ((u64)key << 32) | (u32)(~p);
-      spl[pos] = p;
-    }
+    if (sel) skeys[base + __popc(m & ((1u << (tid & 31)) - 1u))] = ((u64)key << 32) | (u32)(~p);
+  };
+  if (ITEMS > 0) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) compact(i, tid + i * blockDim.x);
+  } else {
+    for (int i = 0; i < n_iter; ++i) compact(i, tid + i * blockDim.x);
   }
-  for (int i = k + tid; i < n_pow2; i += blockDim.x) {
-    skeys[i] = 0;
-    spl[i] = 0;
-  }
+  for (int i = k_sel + tid; i < n_pow2; i += blockDim.x) skeys[i] = 0;
   __syncthreads();
-  bitonic_sort_desc(skeys, spl, n_pow2);
-  // ---- gather: re-decode the k selected boxes into processing order ----
+  bitonic_sort_desc_u64(skeys, n_pow2);
+  // ---- gather: re-decode the selected boxes into processing order ----
   const size_t hw = (size_t)g.H * g.W;
-  const float* fg = cls_prob + (size_t)b * pg.cls_img_stride + pg.cls_fg_offset;
-  const float* deltas = bbox_pred + (size_t)b * 4 * g.A * hw;
-  const float im_h = __ldg(im_info + b * 3), im_w = __ldg(im_info + b * 3 + 1);
-  for (int i = tid; i < k; i += blockDim.x) {
-    const int p = (int)spl[i];
+  const float* fg = tc.cls_prob + (size_t)b * pg.cls_img_stride + pg.cls_fg_offset;
+  const float* deltas = tc.bbox_pred + (size_t)b * 4 * g.A * hw;
+  const float im_h = __ldg(tc.im_info + b * 3), im_w = __ldg(tc.im_info + b * 3 + 1);
+  for (int i = tid; i < k_sel; i += blockDim.x) {
+    const int p = (int)(~(u32)skeys[i]);
     const int a = p % g.A, r = p / g.A;
     const int h = r / g.wc, w = r - h * g.wc;
     double bx[4];
@@ -177,6 +185,18 @@ __global__ void __launch_bounds__(1024) topk_sort_kernel(ProposalGeom pg, Anchor
     ta.score[o] = s;
     ta.orig[o] = p;
   }
+}
+
+// grid B, block 1024.  gated != 0: skip images that already finished NMS.
+template <int ITEMS>
+__global__ void __launch_bounds__(1024) topk_kernel(TopkCall tc, AnchorTable at, int k_limit, int gated,
+                                                    Ctrl* __restrict__ ctrl) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ u32 st[8];
+  __shared__ int s_cnt;
+  const int b = blockIdx.x;
+  if (gated && ctrl[b].done) return;
+  topk_body<ITEMS>(tc, at, k_limit, ctrl, b, smem_raw, st, &s_cnt);
 }
 
 }  // namespace mxr

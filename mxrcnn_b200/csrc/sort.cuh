@@ -34,6 +34,26 @@ static __device__ void bitonic_sort_desc(u64* keys, u32* pl, int n_pow2) {
   }
 }
 
+// Same for bare 64-bit keys that are already distinct (proposal path: score key << 32 | ~row).
+static __device__ void bitonic_sort_desc_u64(u64* keys, int n_pow2) {
+  const int half = n_pow2 >> 1;
+  for (int size = 2; size <= n_pow2; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = threadIdx.x; t < half; t += blockDim.x) {
+        const int i = 2 * t - (t & (stride - 1));
+        const int l = i + stride;
+        const u64 ki = keys[i], kl = keys[l];
+        const bool desc_block = (i & size) == 0;
+        if ((kl > ki) == desc_block) {
+          keys[i] = kl;
+          keys[l] = ki;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
 // Per-warp private 256-bin histograms (no atomics: lanes with the same digit are grouped
 // with match.any and the group's leader adds the group's size).
 __device__ __forceinline__ void warp_hist_add(u32* warp_hist, bool valid, u32 digit) {
@@ -46,28 +66,38 @@ __device__ __forceinline__ void warp_hist_add(u32* warp_hist, bool valid, u32 di
 }
 
 // Radix select on 64-bit composites: finds the threshold T such that exactly `k` valid
-// composites are >= T (composites are distinct).  `compose(q, &c)` returns false for
-// invalid entries.  Needs blockDim.x/32 * 256 u32 of shared scratch (`hist`) and 8 u32 of
-// shared state (`st`).  All threads must call; returns T to every thread.
-template <typename Compose>
-__device__ u64 block_radix_select(int n_items, int k, u32* hist, u32* st, Compose compose) {
+// composites are >= T (composites are distinct).  The items of the CTA are enumerated as
+// (i, q = threadIdx.x + i*blockDim.x), i < n_iter; `compose(i, q, &c)` returns false for invalid
+// / out-of-range entries.  ITEMS > 0 makes the loop a compile-time unrolled one (keys held in
+// registers by the caller), ITEMS == 0 iterates n_iter times.  Needs blockDim.x/32 * 256 u32 of
+// shared scratch (`hist`) and 8 u32 of shared state (`st`).  All threads must call; returns T
+// to every thread.
+template <int ITEMS, typename Compose>
+__device__ __forceinline__ u64 block_radix_select(int n_iter, int k, u32* hist, u32* st, Compose compose) {
   const int nwarps = blockDim.x >> 5;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   u64 prefix = 0;
   int k_rem = k;
-  // iterate over a range rounded up to the block size so that every lane of every warp
-  // reaches the warp-synchronous histogram update
-  const int n_round = (n_items + blockDim.x - 1) / blockDim.x * blockDim.x;
   for (int pass = 0; pass < 8; ++pass) {
     const int shift = 56 - 8 * pass;
     for (int i = threadIdx.x; i < nwarps * 256; i += blockDim.x) hist[i] = 0;
     __syncthreads();
     u32* wh = hist + warp * 256;
-    for (int q = threadIdx.x; q < n_round; q += blockDim.x) {
-      u64 c = 0;
-      bool valid = (q < n_items) && compose(q, &c);
-      if (valid && pass > 0) valid = ((c ^ prefix) >> (shift + 8)) == 0;
-      warp_hist_add(wh, valid, (u32)(c >> shift) & 255u);
+    if (ITEMS > 0) {
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        u64 c = 0;
+        bool valid = compose(i, (int)(threadIdx.x + i * blockDim.x), &c);
+        if (valid && pass > 0) valid = ((c ^ prefix) >> (shift + 8)) == 0;
+        warp_hist_add(wh, valid, (u32)(c >> shift) & 255u);
+      }
+    } else {
+      for (int i = 0; i < n_iter; ++i) {
+        u64 c = 0;
+        bool valid = compose(i, (int)(threadIdx.x + i * blockDim.x), &c);
+        if (valid && pass > 0) valid = ((c ^ prefix) >> (shift + 8)) == 0;
+        warp_hist_add(wh, valid, (u32)(c >> shift) & 255u);
+      }
     }
     __syncthreads();
     // reduce the per-warp histograms into hist[0..255]
