@@ -138,6 +138,41 @@ int mxr_nms_host(mxr_handle_t h, const void* dets, int n, int dtype, double thre
 int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_t* offsets, int n_problems, int dtype,
                     double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out);
 
+/* ---- A2  helper/processing/bbox_transform.py:35-78  bbox_pred(boxes, box_deltas) -------- */
+/* boxes (n,4) f32|f64 (cast to f64 like :46), deltas (n,c4) f32|f64 (exp evaluated in that dtype),
+ * out (n,c4) f64.  n == 0 is a no-op (:43-44).  *_host: all pointers host. */
+int mxr_bbox_pred(mxr_handle_t h, void* stream, const void* boxes, int boxes_dtype, const void* deltas,
+                  int deltas_dtype, int n, int c4, double* out);
+int mxr_bbox_pred_host(mxr_handle_t h, const void* boxes, int boxes_dtype, const void* deltas, int deltas_dtype, int n,
+                       int c4, double* out);
+
+/* ---- A3  helper/processing/bbox_transform.py:81-96  clip_boxes(boxes, im_shape), in place -- */
+/* lim_x = im_shape[1]-1, lim_y = im_shape[0]-1, evaluated by the caller with numpy's scalar rules. */
+int mxr_clip_boxes(mxr_handle_t h, void* stream, void* boxes, int dtype, int n, int c4, double lim_x, double lim_y);
+int mxr_clip_boxes_host(mxr_handle_t h, void* boxes, int dtype, int n, int c4, double lim_x, double lim_y);
+
+/* ---- A10 helper/processing/bbox_transform.py:8-32  bbox_transform(ex_rois, gt_rois) -------- */
+/* ex, gt, out: (n,4) of `dtype` (the promoted dtype of the reference's inputs). */
+int mxr_bbox_transform(mxr_handle_t h, void* stream, const void* ex, const void* gt, int dtype, int n, void* out);
+int mxr_bbox_transform_host(mxr_handle_t h, const void* ex, const void* gt, int dtype, int n, void* out);
+
+/* ---- A7  helper/processing/bbox_regression.py:11-31  bbox_overlaps(boxes, query_boxes) ----- */
+/* f64 IoU with +1 widths; strides are in elements (>= 4; only columns 0..3 are read).  Fused with
+ * the reductions its callers take (rcnn/minibatch.py:296-300, rcnn/rpn/proposal_target.py:143-144):
+ * out (n,k) | row_argmax (n) first maximum | row_max (n) | col_max (k); any of them may be NULL. */
+int mxr_bbox_overlaps(mxr_handle_t h, void* stream, const double* boxes, int n, int box_stride, const double* query,
+                      int k, int query_stride, double* out, int32_t* row_argmax, double* row_max, double* col_max);
+int mxr_bbox_overlaps_host(mxr_handle_t h, const double* boxes, int n, int box_stride, const double* query, int k,
+                           int query_stride, double* out, int32_t* row_argmax, double* row_max, double* col_max);
+
+/* ---- A9  helper/processing/bbox_regression.py:67-85  expand_bbox_regression_targets -------- */
+/* data (k,5) f32 [cls,dx,dy,dw,dh] -> targets, weights (k,4*num_classes) f32.
+ * inside_weights4: HOST, config.TRAIN.BBOX_INSIDE_WEIGHTS. */
+int mxr_expand_bbox_targets(mxr_handle_t h, void* stream, const float* data, int k, int num_classes,
+                            const float* inside_weights4, float* targets, float* weights);
+int mxr_expand_bbox_targets_host(mxr_handle_t h, const float* data, int k, int num_classes, const float* inside_weights4,
+                                 float* targets, float* weights);
+
 /* ---- nms without any allocation (no counterpart in the reference) --------------------- */
 /* Same result as mxr_nms on device arrays, for callers that cannot allocate GPU memory: a plug-in
  * inside a framework whose pool already owns the whole device (a cudaMalloc of ours would fail or

@@ -59,6 +59,20 @@ SIGNATURES = {
     "mxr_nms_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
     "mxr_nms_batched": (ctypes.c_int, [_VP, _VP, _VP, c_int_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                        ctypes.c_int, _VP, _VP]),
+    "mxr_bbox_pred": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, _VP]),
+    "mxr_bbox_pred_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, _VP]),
+    "mxr_clip_boxes": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                      ctypes.c_double]),
+    "mxr_clip_boxes_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                           ctypes.c_double]),
+    "mxr_bbox_transform": (ctypes.c_int, [_VP, _VP, _VP, _VP, ctypes.c_int, ctypes.c_int, _VP]),
+    "mxr_bbox_transform_host": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, _VP]),
+    "mxr_bbox_overlaps": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int,
+                                         _VP, _VP, _VP, _VP]),
+    "mxr_bbox_overlaps_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int,
+                                              _VP, _VP, _VP, _VP]),
+    "mxr_expand_bbox_targets": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, c_float_p, _VP, _VP]),
+    "mxr_expand_bbox_targets_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, c_float_p, _VP, _VP]),
     "mxr_nms_noalloc": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
 }
 

@@ -1,0 +1,184 @@
+// Kernels of the box helpers (helper/processing/bbox_transform.py, bbox_regression.py).
+#pragma once
+#include "device_math.cuh"
+
+namespace mxr {
+
+template <typename T>
+__device__ __forceinline__ T exp_as_numpy(T v);
+template <>
+__device__ __forceinline__ float exp_as_numpy<float>(float v) { return expf(v); }
+template <>
+__device__ __forceinline__ double exp_as_numpy<double>(double v) { return exp(v); }
+
+template <typename T>
+__device__ __forceinline__ T log_as_numpy(T v);
+template <>
+__device__ __forceinline__ float log_as_numpy<float>(float v) { return logf(v); }
+template <>
+__device__ __forceinline__ double log_as_numpy<double>(double v) { return log(v); }
+
+// helper/processing/bbox_transform.py:35-78.  One thread per (row, class).  Boxes are cast to
+// float64 (:46); exp is evaluated in the dtype of the deltas (:67-68), everything else in f64.
+template <typename BT, typename DT>
+__global__ void __launch_bounds__(256) bbox_pred_kernel(const BT* __restrict__ boxes, const DT* __restrict__ deltas, int n,
+                                                        int c4, double* __restrict__ out) {
+  typedef Ar<double> A;
+  const int nc = c4 >> 2;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)n * nc) return;
+  const int i = (int)(t / nc), c = (int)(t - (long long)i * nc);
+  const double x1 = (double)boxes[(size_t)i * 4], y1 = (double)boxes[(size_t)i * 4 + 1];
+  const double x2 = (double)boxes[(size_t)i * 4 + 2], y2 = (double)boxes[(size_t)i * 4 + 3];
+  const double w = A::add(A::sub(x2, x1), 1.0), h = A::add(A::sub(y2, y1), 1.0);
+  const double cx = A::add(x1, A::mul(0.5, A::sub(w, 1.0))), cy = A::add(y1, A::mul(0.5, A::sub(h, 1.0)));
+  const DT* d = deltas + (size_t)i * c4 + 4 * c;
+  const DT dx = d[0], dy = d[1], dw = d[2], dh = d[3];
+  const double pcx = A::add(A::mul((double)dx, w), cx), pcy = A::add(A::mul((double)dy, h), cy);
+  const double pw = A::mul((double)exp_as_numpy<DT>(dw), w), ph = A::mul((double)exp_as_numpy<DT>(dh), h);
+  const double hx = A::mul(0.5, A::sub(pw, 1.0)), hy = A::mul(0.5, A::sub(ph, 1.0));
+  double* o = out + (size_t)i * c4 + 4 * c;
+  o[0] = A::sub(pcx, hx);
+  o[1] = A::sub(pcy, hy);
+  o[2] = A::add(pcx, hx);
+  o[3] = A::add(pcy, hy);
+}
+
+// helper/processing/bbox_transform.py:81-96, in place: max(min(v, lim), 0); x columns use lim_x.
+template <typename T>
+__global__ void __launch_bounds__(256) clip_boxes_kernel(T* __restrict__ boxes, long long total, T lim_x, T lim_y) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= total) return;
+  const T lim = (e & 1) ? lim_y : lim_x;  // row length is a multiple of 4, so column parity == element parity
+  boxes[e] = Ar<T>::vmax(Ar<T>::vmin(boxes[e], lim), T(0));
+}
+
+// helper/processing/bbox_transform.py:8-32 for one (ex, gt) pair, arithmetic in T.
+template <typename T>
+__device__ __forceinline__ void bbox_transform_one(T e0, T e1, T e2, T e3, T g0, T g1, T g2, T g3, T out[4]) {
+  typedef Ar<T> A;
+  const T ew = A::add(A::sub(e2, e0), T(1)), eh = A::add(A::sub(e3, e1), T(1));
+  const T ecx = A::add(e0, A::mul(T(0.5), A::sub(ew, T(1)))), ecy = A::add(e1, A::mul(T(0.5), A::sub(eh, T(1))));
+  const T gw = A::add(A::sub(g2, g0), T(1)), gh = A::add(A::sub(g3, g1), T(1));
+  const T gcx = A::add(g0, A::mul(T(0.5), A::sub(gw, T(1)))), gcy = A::add(g1, A::mul(T(0.5), A::sub(gh, T(1))));
+  out[0] = A::div(A::sub(gcx, ecx), A::add(ew, T(1e-14)));
+  out[1] = A::div(A::sub(gcy, ecy), A::add(eh, T(1e-14)));
+  out[2] = log_as_numpy<T>(A::div(gw, ew));
+  out[3] = log_as_numpy<T>(A::div(gh, eh));
+}
+
+// gt row of pair i is gt_index ? gt_index[i] : i.
+template <typename T>
+__global__ void __launch_bounds__(256) bbox_transform_kernel(const T* __restrict__ ex, int ex_stride, const T* __restrict__ gt,
+                                                             int gt_stride, const int* __restrict__ gt_index, int n,
+                                                             T* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const T* e = ex + (size_t)i * ex_stride;
+  const T* g = gt + (size_t)(gt_index ? gt_index[i] : i) * gt_stride;
+  T o[4];
+  bbox_transform_one<T>(e[0], e[1], e[2], e[3], g[0], g[1], g[2], g[3], o);
+  for (int k = 0; k < 4; ++k) out[(size_t)i * 4 + k] = o[k];
+}
+
+// helper/processing/bbox_regression.py:22-30 for one pair (f64, the reference's operation order).
+__device__ __forceinline__ double overlap_one(double bx1, double by1, double bx2, double by2, double qx1, double qy1, double qx2,
+                                              double qy2, double qarea) {
+  typedef Ar<double> A;
+  const double iw = A::add(A::sub(fmin(bx2, qx2), fmax(bx1, qx1)), 1.0);
+  if (!(iw > 0.0)) return 0.0;
+  const double ih = A::add(A::sub(fmin(by2, qy2), fmax(by1, qy1)), 1.0);
+  if (!(ih > 0.0)) return 0.0;
+  const double barea = A::mul(A::add(A::sub(bx2, bx1), 1.0), A::add(A::sub(by2, by1), 1.0));
+  const double inter = A::mul(iw, ih);
+  return A::div(inter, A::sub(A::add(barea, qarea), inter));
+}
+
+struct OverlapArgs {
+  const double* boxes;   // (n, box_stride), columns 0..3 read
+  int box_stride, n;
+  const double* query;   // (k, query_stride)
+  int query_stride, k;
+  double* out;           // (n,k) or null
+  int* row_argmax;       // (n) or null   -- overlaps.argmax(axis=1): first maximum
+  double* row_max;       // (n) or null
+  double* col_max;       // (k) or null, zero-initialised by the caller (overlaps are >= 0)
+};
+
+static const int kOvChunk = 256;
+
+// bbox_overlaps fused with its consumers' reductions (rcnn/minibatch.py:295-300,
+// rcnn/rpn/proposal_target.py:140-144).  One thread per box row; query boxes staged through
+// shared memory; the column max is a warp shuffle-reduce on the ordered bit pattern of the
+// (non-negative) doubles followed by one atomicMax per warp and column.
+__global__ void __launch_bounds__(128) overlaps_kernel(OverlapArgs a) {
+  __shared__ double sq[kOvChunk][5];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < a.n;
+  double bx1 = 0, by1 = 0, bx2 = 0, by2 = 0;
+  if (live) {
+    const double* b = a.boxes + (size_t)i * a.box_stride;
+    bx1 = b[0];
+    by1 = b[1];
+    bx2 = b[2];
+    by2 = b[3];
+  }
+  double best = 0.0;
+  int arg = 0;
+  for (int q0 = 0; q0 < a.k; q0 += kOvChunk) {
+    const int qn = min(kOvChunk, a.k - q0);
+    __syncthreads();
+    for (int t = threadIdx.x; t < qn; t += blockDim.x) {
+      const double* q = a.query + (size_t)(q0 + t) * a.query_stride;
+      const double x1 = q[0], y1 = q[1], x2 = q[2], y2 = q[3];
+      sq[t][0] = x1;
+      sq[t][1] = y1;
+      sq[t][2] = x2;
+      sq[t][3] = y2;
+      sq[t][4] = Ar<double>::mul(Ar<double>::add(Ar<double>::sub(x2, x1), 1.0), Ar<double>::add(Ar<double>::sub(y2, y1), 1.0));
+    }
+    __syncthreads();
+    for (int j = 0; j < qn; ++j) {
+      const double ov = live ? overlap_one(bx1, by1, bx2, by2, sq[j][0], sq[j][1], sq[j][2], sq[j][3], sq[j][4]) : 0.0;
+      if (live) {
+        if (a.out) a.out[(size_t)i * a.k + q0 + j] = ov;
+        if ((q0 + j == 0) || ov > best) {
+          best = ov;
+          arg = q0 + j;
+        }
+      }
+      if (a.col_max) {
+        unsigned long long bits = (unsigned long long)__double_as_longlong(ov);
+        for (int o = 16; o > 0; o >>= 1) {
+          const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o);
+          bits = other > bits ? other : bits;
+        }
+        if ((threadIdx.x & 31) == 0 && bits != 0ull) atomicMax(reinterpret_cast<unsigned long long*>(a.col_max) + q0 + j, bits);
+      }
+    }
+  }
+  if (live) {
+    if (a.row_argmax) a.row_argmax[i] = arg;
+    if (a.row_max) a.row_max[i] = best;
+  }
+}
+
+// helper/processing/bbox_regression.py:67-85.  One thread per (row, class slot).
+__global__ void __launch_bounds__(256) expand_targets_kernel(const float* __restrict__ data, int k, int num_classes, float4 iw,
+                                                             float* __restrict__ targets, float* __restrict__ weights) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)k * num_classes) return;
+  const int row = (int)(t / num_classes), c = (int)(t - (long long)row * num_classes);
+  const float cls = data[(size_t)row * 5];
+  const int start = cls > 0.f ? (int)(4.f * cls) : -1000;  // int(4 * cls), :81
+  const float w4[4] = {iw.x, iw.y, iw.z, iw.w};
+  for (int e = 0; e < 4; ++e) {
+    const int col = 4 * c + e;
+    const int off = col - start;
+    const bool hit = off >= 0 && off < 4;
+    targets[(size_t)row * 4 * num_classes + col] = hit ? data[(size_t)row * 5 + 1 + off] : 0.f;
+    weights[(size_t)row * 4 * num_classes + col] = hit ? w4[off] : 0.f;
+  }
+}
+
+}  // namespace mxr
