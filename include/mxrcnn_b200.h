@@ -152,9 +152,11 @@ int mxr_clip_boxes(mxr_handle_t h, void* stream, void* boxes, int dtype, int n, 
 int mxr_clip_boxes_host(mxr_handle_t h, void* boxes, int dtype, int n, int c4, double lim_x, double lim_y);
 
 /* ---- A10 helper/processing/bbox_transform.py:8-32  bbox_transform(ex_rois, gt_rois) -------- */
-/* ex, gt, out: (n,4) of `dtype` (the promoted dtype of the reference's inputs). */
-int mxr_bbox_transform(mxr_handle_t h, void* stream, const void* ex, const void* gt, int dtype, int n, void* out);
-int mxr_bbox_transform_host(mxr_handle_t h, const void* ex, const void* gt, int dtype, int n, void* out);
+/* ex (n,4) and gt (n,4) each f32|f64; numpy computes each side in its own dtype and the targets in
+ * the promoted one, so out (n,4) is f32 only when both inputs are f32, else f64. */
+int mxr_bbox_transform(mxr_handle_t h, void* stream, const void* ex, int ex_dtype, const void* gt, int gt_dtype, int n,
+                       void* out);
+int mxr_bbox_transform_host(mxr_handle_t h, const void* ex, int ex_dtype, const void* gt, int gt_dtype, int n, void* out);
 
 /* ---- A7  helper/processing/bbox_regression.py:11-31  bbox_overlaps(boxes, query_boxes) ----- */
 /* f64 IoU with +1 widths; strides are in elements (>= 4; only columns 0..3 are read).  Fused with
@@ -172,6 +174,63 @@ int mxr_expand_bbox_targets(mxr_handle_t h, void* stream, const float* data, int
                             const float* inside_weights4, float* targets, float* weights);
 int mxr_expand_bbox_targets_host(mxr_handle_t h, const float* data, int k, int num_classes, const float* inside_weights4,
                                  float* targets, float* weights);
+
+/* ---- A6  rcnn/minibatch.py:204-395  assign_anchor ---------------------------------------- */
+/* Two phases around the reference's RNG draws (minibatch.py:319-334).
+ * phase1 (synchronous): inside filter, IoU vs gt, argmax / gt_argmax labels (quirk Q4), ordered fg / bg
+ *   lists.  anchors: HOST (A,4) f64 from mxr_generate_anchors(16, ratios, float32 scales);
+ *   gt_boxes: HOST (G,5) f32; counts_out: HOST [n_inside, n_fg, n_bg] (labels==1 / ==0 before subsampling).
+ * The caller draws, in this order and only when over quota, the fg then bg ranks to disable:
+ *   npr.choice(fg_inds, size=k, replace=False) == fg_inds[npr.permutation(n_fg)[:k]]  -> pass the RANKS.
+ * phase2: applies the draws and writes, in the reference's output layouts,
+ *   label (A*H*W) f32 in (a,h,w) order; bbox_target / inside / outside weights (4A,H,W) f32, channel a*4+k.
+ *   positive_weight / negative_weight: the values of minibatch.py:343-354 computed by the caller.
+ * State lives in the handle between the two calls (no other anchor-target call in between). */
+typedef struct {
+  int feat_height, feat_width, num_anchors;
+  int feat_stride;      /* python int, minibatch.py:260 */
+  int allowed_border;
+  float im_height, im_width; /* im_info[0][0], im_info[0][1] */
+  int num_gt;
+  double negative_overlap, positive_overlap; /* RPN_NEGATIVE_OVERLAP, RPN_POSITIVE_OVERLAP */
+  int clobber_positives;
+} mxr_anchor_target_params;
+int mxr_anchor_target_phase1(mxr_handle_t h, const mxr_anchor_target_params* p, const double* anchors,
+                             const float* gt_boxes, int32_t* counts_out);
+int mxr_anchor_target_phase2(mxr_handle_t h, void* stream, const int32_t* fg_disable_ranks, int n_fg_disable,
+                             const int32_t* bg_disable_ranks, int n_bg_disable, double positive_weight,
+                             double negative_weight, const float* inside_weights4, float* label, float* bbox_target,
+                             float* bbox_inside_weight, float* bbox_outside_weight);
+int mxr_anchor_target_phase2_host(mxr_handle_t h, const int32_t* fg_disable_ranks, int n_fg_disable,
+                                  const int32_t* bg_disable_ranks, int n_bg_disable, double positive_weight,
+                                  double negative_weight, const float* inside_weights4, float* label,
+                                  float* bbox_target, float* bbox_inside_weight, float* bbox_outside_weight);
+
+/* ---- A8/A11  rcnn/rpn/proposal_target.py:148,160-161 and rcnn/minibatch.py:166,174 ---------- */
+/* fg_list = where(ov >= fg_thresh), bg_list = where((ov < bg_hi) & (ov >= bg_lo)), ascending, compared
+ * in the dtype of `overlaps` (f64 from bbox_overlaps, f32 from a roidb).  counts: [n_fg, n_bg]. */
+int mxr_fg_bg_lists(mxr_handle_t h, void* stream, const void* overlaps, int dtype, int n, double fg_thresh, double bg_hi,
+                    double bg_lo, int32_t* fg_list, int32_t* bg_list, int32_t* counts);
+int mxr_fg_bg_lists_host(mxr_handle_t h, const void* overlaps, int dtype, int n, double fg_thresh, double bg_hi,
+                         double bg_lo, int32_t* fg_list, int32_t* bg_list, int32_t* counts);
+
+/* ---- A8  rcnn/rpn/proposal_target.py:183-194,120-133 -------------------------------------- */
+/* Given the sampled roi indices (drawn by the caller, proposal_target.py:153-180): gather rois, labels
+ * (zeroed from fg_this on, quirk Q3), float32 bbox_transform targets, optional (t-mean)/std in f64,
+ * class-expanded targets and inside / outside weights.  rois (R,5) f32, gt_boxes (G,5) f32,
+ * gt_assignment (R) i32, keep_inds (K) i32 -> out_rois (K,5), labels (K), three (K,4C) maps. */
+typedef struct {
+  int num_rois, num_gt, num_keep, fg_this, num_classes;
+  int normalize;        /* config.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED */
+  double means[4], stds[4];
+  float inside_weights[4];
+} mxr_proposal_target_params;
+int mxr_proposal_target_gather(mxr_handle_t h, void* stream, const mxr_proposal_target_params* p, const float* rois,
+                               const float* gt_boxes, const int32_t* gt_assignment, const int32_t* keep_inds,
+                               float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside);
+int mxr_proposal_target_gather_host(mxr_handle_t h, const mxr_proposal_target_params* p, const float* rois,
+                                    const float* gt_boxes, const int32_t* gt_assignment, const int32_t* keep_inds,
+                                    float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside);
 
 /* ---- nms without any allocation (no counterpart in the reference) --------------------- */
 /* Same result as mxr_nms on device arrays, for callers that cannot allocate GPU memory: a plug-in

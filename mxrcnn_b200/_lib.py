@@ -33,6 +33,19 @@ class ProposalParams(ctypes.Structure):
                 ("nms_thresh", ctypes.c_double), ("min_size", ctypes.c_float), ("first_stripe", ctypes.c_int)]
 
 
+class AnchorTargetParams(ctypes.Structure):
+    _fields_ = [("feat_height", ctypes.c_int), ("feat_width", ctypes.c_int), ("num_anchors", ctypes.c_int),
+                ("feat_stride", ctypes.c_int), ("allowed_border", ctypes.c_int), ("im_height", ctypes.c_float),
+                ("im_width", ctypes.c_float), ("num_gt", ctypes.c_int), ("negative_overlap", ctypes.c_double),
+                ("positive_overlap", ctypes.c_double), ("clobber_positives", ctypes.c_int)]
+
+
+class ProposalTargetParams(ctypes.Structure):
+    _fields_ = [("num_rois", ctypes.c_int), ("num_gt", ctypes.c_int), ("num_keep", ctypes.c_int),
+                ("fg_this", ctypes.c_int), ("num_classes", ctypes.c_int), ("normalize", ctypes.c_int),
+                ("means", ctypes.c_double * 4), ("stds", ctypes.c_double * 4), ("inside_weights", ctypes.c_float * 4)]
+
+
 # every symbol include/mxrcnn_b200.h declares: name -> (restype, argtypes)
 _VP = ctypes.c_void_p
 SIGNATURES = {
@@ -65,14 +78,25 @@ SIGNATURES = {
                                       ctypes.c_double]),
     "mxr_clip_boxes_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                            ctypes.c_double]),
-    "mxr_bbox_transform": (ctypes.c_int, [_VP, _VP, _VP, _VP, ctypes.c_int, ctypes.c_int, _VP]),
-    "mxr_bbox_transform_host": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, _VP]),
+    "mxr_bbox_transform": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, _VP]),
+    "mxr_bbox_transform_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, _VP]),
     "mxr_bbox_overlaps": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int,
                                          _VP, _VP, _VP, _VP]),
     "mxr_bbox_overlaps_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int,
                                               _VP, _VP, _VP, _VP]),
     "mxr_expand_bbox_targets": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, c_float_p, _VP, _VP]),
     "mxr_expand_bbox_targets_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, c_float_p, _VP, _VP]),
+    "mxr_anchor_target_phase1": (ctypes.c_int, [_VP, _VP, c_double_p, _VP, c_int_p]),
+    "mxr_anchor_target_phase2": (ctypes.c_int, [_VP, _VP, c_int_p, ctypes.c_int, c_int_p, ctypes.c_int, ctypes.c_double,
+                                                ctypes.c_double, c_float_p, _VP, _VP, _VP, _VP]),
+    "mxr_anchor_target_phase2_host": (ctypes.c_int, [_VP, c_int_p, ctypes.c_int, c_int_p, ctypes.c_int, ctypes.c_double,
+                                                     ctypes.c_double, c_float_p, _VP, _VP, _VP, _VP]),
+    "mxr_fg_bg_lists": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                                       ctypes.c_double, _VP, _VP, _VP]),
+    "mxr_fg_bg_lists_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                                            ctypes.c_double, _VP, _VP, _VP]),
+    "mxr_proposal_target_gather": (ctypes.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "mxr_proposal_target_gather_host": (ctypes.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "mxr_nms_noalloc": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
 }
 

@@ -1,5 +1,6 @@
 // C ABI of libmxrcnn_b200.so: handle / workspace management and error reporting.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -80,6 +81,7 @@ int mxr_destroy(mxr_handle_t hh) {
   cudaDeviceSynchronize();
   if (h->d_ws) cudaFree(h->d_ws);
   if (h->h_pin) cudaFreeHost(h->h_pin);
+  if (h->at_state) free(h->at_state);
   if (h->ev) cudaEventDestroy(h->ev);
   if (h->prof) {
     for (int i = 0; i < h->prof_cap; ++i) {

@@ -53,31 +53,37 @@ __global__ void __launch_bounds__(256) clip_boxes_kernel(T* __restrict__ boxes, 
   boxes[e] = Ar<T>::vmax(Ar<T>::vmin(boxes[e], lim), T(0));
 }
 
-// helper/processing/bbox_transform.py:8-32 for one (ex, gt) pair, arithmetic in T.
-template <typename T>
-__device__ __forceinline__ void bbox_transform_one(T e0, T e1, T e2, T e3, T g0, T g1, T g2, T g3, T out[4]) {
-  typedef Ar<T> A;
-  const T ew = A::add(A::sub(e2, e0), T(1)), eh = A::add(A::sub(e3, e1), T(1));
-  const T ecx = A::add(e0, A::mul(T(0.5), A::sub(ew, T(1)))), ecy = A::add(e1, A::mul(T(0.5), A::sub(eh, T(1))));
-  const T gw = A::add(A::sub(g2, g0), T(1)), gh = A::add(A::sub(g3, g1), T(1));
-  const T gcx = A::add(g0, A::mul(T(0.5), A::sub(gw, T(1)))), gcy = A::add(g1, A::mul(T(0.5), A::sub(gh, T(1))));
-  out[0] = A::div(A::sub(gcx, ecx), A::add(ew, T(1e-14)));
-  out[1] = A::div(A::sub(gcy, ecy), A::add(eh, T(1e-14)));
-  out[2] = log_as_numpy<T>(A::div(gw, ew));
-  out[3] = log_as_numpy<T>(A::div(gh, eh));
+// helper/processing/bbox_transform.py:8-32 for one (ex, gt) pair.  numpy evaluates the ex-side
+// quantities (:14-17) in the dtype of ex_rois, the gt-side ones (:19-22) in the dtype of gt_rois,
+// and the four targets (:24-27) in the promoted dtype TO -- e.g. rcnn/minibatch.py:338 passes
+// float64 anchors with float32 gt boxes.
+template <typename TE, typename TG, typename TO>
+__device__ __forceinline__ void bbox_transform_one(TE e0, TE e1, TE e2, TE e3, TG g0, TG g1, TG g2, TG g3, TO out[4]) {
+  typedef Ar<TE> AE;
+  typedef Ar<TG> AG;
+  typedef Ar<TO> AO;
+  const TE ew = AE::add(AE::sub(e2, e0), TE(1)), eh = AE::add(AE::sub(e3, e1), TE(1));
+  const TE ecx = AE::add(e0, AE::mul(TE(0.5), AE::sub(ew, TE(1)))), ecy = AE::add(e1, AE::mul(TE(0.5), AE::sub(eh, TE(1))));
+  const TG gw = AG::add(AG::sub(g2, g0), TG(1)), gh = AG::add(AG::sub(g3, g1), TG(1));
+  const TG gcx = AG::add(g0, AG::mul(TG(0.5), AG::sub(gw, TG(1)))), gcy = AG::add(g1, AG::mul(TG(0.5), AG::sub(gh, TG(1))));
+  // ex_widths + 1e-14 stays in the ex dtype (python float is a weak scalar)
+  out[0] = AO::div(AO::sub((TO)gcx, (TO)ecx), (TO)AE::add(ew, TE(1e-14)));
+  out[1] = AO::div(AO::sub((TO)gcy, (TO)ecy), (TO)AE::add(eh, TE(1e-14)));
+  out[2] = log_as_numpy<TO>(AO::div((TO)gw, (TO)ew));
+  out[3] = log_as_numpy<TO>(AO::div((TO)gh, (TO)eh));
 }
 
 // gt row of pair i is gt_index ? gt_index[i] : i.
-template <typename T>
-__global__ void __launch_bounds__(256) bbox_transform_kernel(const T* __restrict__ ex, int ex_stride, const T* __restrict__ gt,
+template <typename TE, typename TG, typename TO>
+__global__ void __launch_bounds__(256) bbox_transform_kernel(const TE* __restrict__ ex, int ex_stride, const TG* __restrict__ gt,
                                                              int gt_stride, const int* __restrict__ gt_index, int n,
-                                                             T* __restrict__ out) {
+                                                             TO* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const T* e = ex + (size_t)i * ex_stride;
-  const T* g = gt + (size_t)(gt_index ? gt_index[i] : i) * gt_stride;
-  T o[4];
-  bbox_transform_one<T>(e[0], e[1], e[2], e[3], g[0], g[1], g[2], g[3], o);
+  const TE* e = ex + (size_t)i * ex_stride;
+  const TG* g = gt + (size_t)(gt_index ? gt_index[i] : i) * gt_stride;
+  TO o[4];
+  bbox_transform_one<TE, TG, TO>(e[0], e[1], e[2], e[3], g[0], g[1], g[2], g[3], o);
   for (int k = 0; k < 4; ++k) out[(size_t)i * 4 + k] = o[k];
 }
 
@@ -111,7 +117,7 @@ static const int kOvChunk = 256;
 // rcnn/rpn/proposal_target.py:140-144).  One thread per box row; query boxes staged through
 // shared memory; the column max is a warp shuffle-reduce on the ordered bit pattern of the
 // (non-negative) doubles followed by one atomicMax per warp and column.
-__global__ void __launch_bounds__(128) overlaps_kernel(OverlapArgs a) {
+static __global__ void __launch_bounds__(128) overlaps_kernel(OverlapArgs a) {
   __shared__ double sq[kOvChunk][5];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = i < a.n;
@@ -164,7 +170,7 @@ __global__ void __launch_bounds__(128) overlaps_kernel(OverlapArgs a) {
 }
 
 // helper/processing/bbox_regression.py:67-85.  One thread per (row, class slot).
-__global__ void __launch_bounds__(256) expand_targets_kernel(const float* __restrict__ data, int k, int num_classes, float4 iw,
+static __global__ void __launch_bounds__(256) expand_targets_kernel(const float* __restrict__ data, int k, int num_classes, float4 iw,
                                                              float* __restrict__ targets, float* __restrict__ weights) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (long long)k * num_classes) return;

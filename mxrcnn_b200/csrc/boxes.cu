@@ -121,7 +121,8 @@ int mxr_clip_boxes_host(mxr_handle_t hh, void* boxes, int dtype, int n, int c4, 
 }
 
 // ---- bbox_transform ----------------------------------------------------------------------
-int mxr_bbox_transform(mxr_handle_t hh, void* stream, const void* ex, const void* gt, int dtype, int n, void* out) {
+int mxr_bbox_transform(mxr_handle_t hh, void* stream, const void* ex, int ex_dtype, const void* gt, int gt_dtype, int n,
+                       void* out) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_bbox_transform: NULL handle");
   MXR_REQUIRE(n >= 0, MXR_ERR_INVALID, "mxr_bbox_transform: n < 0");
   if (n == 0) return MXR_OK;
@@ -130,13 +131,18 @@ int mxr_bbox_transform(mxr_handle_t hh, void* stream, const void* ex, const void
   MXR_CUDA(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   h->last_launches = 0;
+  const int g = (n + 255) / 256;
   prof_begin(h, s, ST_BOXES);
-  if (dtype == MXR_DTYPE_F64)
-    bbox_transform_kernel<double><<<(n + 255) / 256, 256, 0, s>>>((const double*)ex, 4, (const double*)gt, 4, nullptr, n, (double*)out);
-  else if (dtype == MXR_DTYPE_F32)
-    bbox_transform_kernel<float><<<(n + 255) / 256, 256, 0, s>>>((const float*)ex, 4, (const float*)gt, 4, nullptr, n, (float*)out);
+  if (ex_dtype == MXR_DTYPE_F64 && gt_dtype == MXR_DTYPE_F64)
+    bbox_transform_kernel<double, double, double><<<g, 256, 0, s>>>((const double*)ex, 4, (const double*)gt, 4, nullptr, n, (double*)out);
+  else if (ex_dtype == MXR_DTYPE_F32 && gt_dtype == MXR_DTYPE_F32)
+    bbox_transform_kernel<float, float, float><<<g, 256, 0, s>>>((const float*)ex, 4, (const float*)gt, 4, nullptr, n, (float*)out);
+  else if (ex_dtype == MXR_DTYPE_F64 && gt_dtype == MXR_DTYPE_F32)
+    bbox_transform_kernel<double, float, double><<<g, 256, 0, s>>>((const double*)ex, 4, (const float*)gt, 4, nullptr, n, (double*)out);
+  else if (ex_dtype == MXR_DTYPE_F32 && gt_dtype == MXR_DTYPE_F64)
+    bbox_transform_kernel<float, double, double><<<g, 256, 0, s>>>((const float*)ex, 4, (const double*)gt, 4, nullptr, n, (double*)out);
   else {
-    set_error("mxr_bbox_transform: dtype must be f32 or f64");
+    set_error("mxr_bbox_transform: dtypes must be f32 or f64");
     return MXR_ERR_INVALID;
   }
   prof_end(h, s);
@@ -144,20 +150,22 @@ int mxr_bbox_transform(mxr_handle_t hh, void* stream, const void* ex, const void
   return MXR_OK;
 }
 
-int mxr_bbox_transform_host(mxr_handle_t hh, const void* ex, const void* gt, int dtype, int n, void* out) {
+int mxr_bbox_transform_host(mxr_handle_t hh, const void* ex, int ex_dtype, const void* gt, int gt_dtype, int n, void* out) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_bbox_transform_host: NULL handle");
   if (n <= 0) return n < 0 ? MXR_ERR_INVALID : MXR_OK;
   Handle* h = reinterpret_cast<Handle*>(hh);
   MXR_CUDA(cudaSetDevice(h->device));
-  const size_t bs = (size_t)n * 4 * (dtype == MXR_DTYPE_F64 ? 8 : 4);
+  const size_t es = (size_t)n * 4 * (ex_dtype == MXR_DTYPE_F64 ? 8 : 4);
+  const size_t gs = (size_t)n * 4 * (gt_dtype == MXR_DTYPE_F64 ? 8 : 4);
+  const size_t os = (size_t)n * 4 * ((ex_dtype == MXR_DTYPE_F32 && gt_dtype == MXR_DTYPE_F32) ? 4 : 8);
   Staged st(h);
-  const size_t oe = st.reserve(bs), og = st.reserve(bs), oo = st.reserve(bs);
+  const size_t oe = st.reserve(es), og = st.reserve(gs), oo = st.reserve(os);
   MXR_TRY(ensure_device_ws(h, st.off));
   char* w = h->d_ws;
-  MXR_CUDA(cudaMemcpyAsync(w + oe, ex, bs, cudaMemcpyHostToDevice, st.s));
-  MXR_CUDA(cudaMemcpyAsync(w + og, gt, bs, cudaMemcpyHostToDevice, st.s));
-  MXR_TRY(mxr_bbox_transform(hh, st.s, w + oe, w + og, dtype, n, w + oo));
-  MXR_CUDA(cudaMemcpyAsync(out, w + oo, bs, cudaMemcpyDeviceToHost, st.s));
+  MXR_CUDA(cudaMemcpyAsync(w + oe, ex, es, cudaMemcpyHostToDevice, st.s));
+  MXR_CUDA(cudaMemcpyAsync(w + og, gt, gs, cudaMemcpyHostToDevice, st.s));
+  MXR_TRY(mxr_bbox_transform(hh, st.s, w + oe, ex_dtype, w + og, gt_dtype, n, w + oo));
+  MXR_CUDA(cudaMemcpyAsync(out, w + oo, os, cudaMemcpyDeviceToHost, st.s));
   MXR_CUDA(cudaStreamSynchronize(st.s));
   return MXR_OK;
 }

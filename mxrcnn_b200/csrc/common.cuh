@@ -90,6 +90,7 @@ struct Handle {
   int last_launches;  // kernels launched by the most recent call
   int smem_attr[8];   // largest dynamic-smem opt-in already set per kernel (0 topk, 1 prep f32, 2 prep f64, 3.. coop)
   int coop_grid[4];   // co-resident grid size of the cooperative kernels (0: not queried yet)
+  void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
 };
 
 // Bracket one kernel launch.  No-ops unless mxr_profile_enable(h, 1) was called.

@@ -1,0 +1,311 @@
+// Training-target generators: assign_anchor (rcnn/minibatch.py:204-395) and the device side of
+// _sample_rois / sample_rois (rcnn/rpn/proposal_target.py:135-196, rcnn/minibatch.py:151-201).
+#include <stdlib.h>
+#include <string.h>
+
+#include "target_kernels.cuh"
+
+using namespace mxr;
+
+namespace {
+
+struct AnchorTargetState {
+  AnchorTargetGeom g;
+  AnchorTargetWs w;
+  float* d_gt;       // (G,5) f32 copy of the gt boxes
+  int* d_ranks;      // disable ranks staged for phase 2
+  int ranks_cap;
+  char* d_out;       // staging of the four output maps for the *_host variant
+  bool valid;
+};
+
+size_t at_layout(const AnchorTargetGeom& g, char* base, AnchorTargetState* st) {
+  Carver c(base);
+  const int N = g.N, G = g.G > 0 ? g.G : 1;
+  st->w.counts = c.take<int>(4);
+  st->w.colmax = c.take<double>(G);
+  st->w.inside_rank = c.take<int>(N);
+  st->w.anchors_in = c.take<double>((size_t)N * 4);
+  st->w.gt64 = c.take<double>((size_t)G * 4);
+  st->w.argmax = c.take<int>(N);
+  st->w.maxov = c.take<double>(N);
+  st->w.labels = c.take<float>(N);
+  st->w.fg_list = c.take<int>(N);
+  st->w.bg_list = c.take<int>(N);
+  st->d_gt = c.take<float>((size_t)G * 5);
+  st->ranks_cap = 2 * N;
+  st->d_ranks = c.take<int>(st->ranks_cap);
+  st->d_out = c.take<char>((size_t)N * 13 * sizeof(float));  // label N + 3 maps of 4N
+  return align_up(c.off, 256);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mxr_anchor_target_phase1(mxr_handle_t hh, const mxr_anchor_target_params* p, const double* anchors,
+                             const float* gt_boxes, int32_t* counts_out) {
+  MXR_REQUIRE(hh != nullptr && p != nullptr && anchors != nullptr && counts_out != nullptr, MXR_ERR_INVALID,
+              "mxr_anchor_target_phase1: NULL argument");
+  MXR_REQUIRE(p->feat_height >= 1 && p->feat_width >= 1 && p->num_anchors >= 1 && p->num_anchors <= 64 && p->num_gt >= 0,
+              MXR_ERR_INVALID, "mxr_anchor_target_phase1: bad shape");
+  MXR_REQUIRE(p->num_gt == 0 || gt_boxes != nullptr, MXR_ERR_INVALID, "mxr_anchor_target_phase1: NULL gt_boxes");
+  const long long N = (long long)p->num_anchors * p->feat_height * p->feat_width;
+  MXR_REQUIRE(N <= (1 << 24), MXR_ERR_LIMIT, "mxr_anchor_target_phase1: %lld anchors exceed the maximum of 16777216", N);
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  if (!h->at_state) {
+    h->at_state = calloc(1, sizeof(AnchorTargetState));
+    MXR_REQUIRE(h->at_state != nullptr, MXR_ERR_NOMEM, "mxr_anchor_target_phase1: out of host memory");
+  }
+  AnchorTargetState* st = reinterpret_cast<AnchorTargetState*>(h->at_state);
+  st->valid = false;
+  AnchorTargetGeom& g = st->g;
+  g.fh = p->feat_height;
+  g.fw = p->feat_width;
+  g.A = p->num_anchors;
+  g.N = (int)N;
+  g.feat_stride = p->feat_stride;
+  g.allowed_border = p->allowed_border;
+  g.im_h = p->im_height;
+  g.im_w = p->im_width;
+  g.G = p->num_gt;
+  MXR_TRY(ensure_device_ws(h, at_layout(g, nullptr, st)));
+  at_layout(g, h->d_ws, st);
+  MXR_TRY(ensure_pinned_ws(h, 4 * sizeof(int)));
+  cudaStream_t s = h->stream;
+  AnchorTable at;
+  memset(&at, 0, sizeof(at));
+  memcpy(at.a, anchors, sizeof(double) * 4 * g.A);
+  h->last_launches = 0;
+  // counts and colmax are contiguous at the start of the layout: one memset (overlaps are >= 0)
+  MXR_CUDA(cudaMemsetAsync(st->w.counts, 0, (char*)st->w.inside_rank - (char*)st->w.counts, s));
+  if (g.G > 0) MXR_CUDA(cudaMemcpyAsync(st->d_gt, gt_boxes, (size_t)g.G * 5 * sizeof(float), cudaMemcpyHostToDevice, s));
+  prof_begin(h, s, ST_ANCHOR_TARGET);
+  anchor_inside_kernel<<<1, 1024, 0, s>>>(g, at, st->d_gt, st->w);
+  prof_end(h, s);
+  const int grid = (g.N + 127) / 128;
+  if (g.G > 0) {
+    prof_begin(h, s, ST_ANCHOR_TARGET);
+    anchor_overlaps_kernel<<<grid, 128, 0, s>>>(g, st->w);
+    prof_end(h, s);
+  }
+  prof_begin(h, s, ST_ANCHOR_TARGET);
+  anchor_label_kernel<<<grid, 128, 0, s>>>(g, st->w, p->negative_overlap, p->positive_overlap, p->clobber_positives);
+  prof_end(h, s);
+  prof_begin(h, s, ST_ANCHOR_TARGET);
+  anchor_lists_kernel<<<1, 1024, 0, s>>>(st->w);
+  prof_end(h, s);
+  MXR_CUDA(cudaMemcpyAsync(h->h_pin, st->w.counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaStreamSynchronize(s));
+  memcpy(counts_out, h->h_pin, 3 * sizeof(int));
+  st->valid = true;
+  return MXR_OK;
+}
+
+static int at_phase2(Handle* h, cudaStream_t s, AnchorTargetState* st, const int32_t* fg_ranks, int n_fg, const int32_t* bg_ranks, int n_bg,
+                     double pos_w, double neg_w, const float* iw4, float* label, float* target, float* inside,
+                     float* outside) {
+  const AnchorTargetGeom& g = st->g;
+  MXR_REQUIRE(n_fg >= 0 && n_bg >= 0 && n_fg + n_bg <= st->ranks_cap, MXR_ERR_INVALID,
+              "mxr_anchor_target_phase2: bad disable counts %d/%d", n_fg, n_bg);
+  if (n_fg + n_bg > 0) {
+    MXR_TRY(ensure_pinned_ws(h, (size_t)(n_fg + n_bg) * sizeof(int)));
+    if (n_fg) memcpy(h->h_pin, fg_ranks, (size_t)n_fg * sizeof(int));
+    if (n_bg) memcpy(h->h_pin + (size_t)n_fg * sizeof(int), bg_ranks, (size_t)n_bg * sizeof(int));
+    MXR_CUDA(cudaMemcpyAsync(st->d_ranks, h->h_pin, (size_t)(n_fg + n_bg) * sizeof(int), cudaMemcpyHostToDevice, s));
+    prof_begin(h, s, ST_ANCHOR_TARGET);
+    anchor_disable_kernel<<<(n_fg + n_bg + 255) / 256, 256, 0, s>>>(st->w, st->d_ranks, n_fg, st->d_ranks + n_fg, n_bg);
+    prof_end(h, s);
+  }
+  const float4 iw = make_float4(iw4[0], iw4[1], iw4[2], iw4[3]);
+  prof_begin(h, s, ST_ANCHOR_TARGET);
+  anchor_output_kernel<<<(g.N + 255) / 256, 256, 0, s>>>(g, st->w, st->d_gt, iw, (float)pos_w, (float)neg_w, label, target, inside,
+                                                         outside);
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+int mxr_anchor_target_phase2(mxr_handle_t hh, void* stream, const int32_t* fg_disable_ranks, int n_fg_disable,
+                             const int32_t* bg_disable_ranks, int n_bg_disable, double positive_weight,
+                             double negative_weight, const float* inside_weights4, float* label, float* bbox_target,
+                             float* bbox_inside_weight, float* bbox_outside_weight) {
+  MXR_REQUIRE(hh != nullptr && inside_weights4 && label && bbox_target && bbox_inside_weight && bbox_outside_weight,
+              MXR_ERR_INVALID, "mxr_anchor_target_phase2: NULL argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  AnchorTargetState* st = reinterpret_cast<AnchorTargetState*>(h->at_state);
+  MXR_REQUIRE(st && st->valid, MXR_ERR_INVALID, "mxr_anchor_target_phase2: call mxr_anchor_target_phase1 first");
+  MXR_CUDA(cudaSetDevice(h->device));
+  // phase 1 ran on the handle's stream and was synchronised, so its results are visible to any stream
+  MXR_TRY(at_phase2(h, (cudaStream_t)stream, st, fg_disable_ranks, n_fg_disable, bg_disable_ranks, n_bg_disable, positive_weight,
+                    negative_weight, inside_weights4, label, bbox_target, bbox_inside_weight, bbox_outside_weight));
+  st->valid = false;
+  return MXR_OK;
+}
+
+int mxr_anchor_target_phase2_host(mxr_handle_t hh, const int32_t* fg_disable_ranks, int n_fg_disable,
+                                  const int32_t* bg_disable_ranks, int n_bg_disable, double positive_weight,
+                                  double negative_weight, const float* inside_weights4, float* label, float* bbox_target,
+                                  float* bbox_inside_weight, float* bbox_outside_weight) {
+  MXR_REQUIRE(hh != nullptr && inside_weights4 && label && bbox_target && bbox_inside_weight && bbox_outside_weight,
+              MXR_ERR_INVALID, "mxr_anchor_target_phase2_host: NULL argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  AnchorTargetState* st = reinterpret_cast<AnchorTargetState*>(h->at_state);
+  MXR_REQUIRE(st && st->valid, MXR_ERR_INVALID, "mxr_anchor_target_phase2_host: call mxr_anchor_target_phase1 first");
+  MXR_CUDA(cudaSetDevice(h->device));
+  const size_t N = st->g.N;
+  float* d = reinterpret_cast<float*>(st->d_out);
+  cudaStream_t s = h->stream;
+  MXR_TRY(at_phase2(h, s, st, fg_disable_ranks, n_fg_disable, bg_disable_ranks, n_bg_disable, positive_weight, negative_weight,
+                    inside_weights4, d, d + N, d + 5 * N, d + 9 * N));
+  MXR_CUDA(cudaMemcpyAsync(label, d, N * 4, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaMemcpyAsync(bbox_target, d + N, 4 * N * 4, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaMemcpyAsync(bbox_inside_weight, d + 5 * N, 4 * N * 4, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaMemcpyAsync(bbox_outside_weight, d + 9 * N, 4 * N * 4, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaStreamSynchronize(s));
+  st->valid = false;
+  return MXR_OK;
+}
+
+// ---- fg / bg candidate lists -------------------------------------------------------------
+int mxr_fg_bg_lists(mxr_handle_t hh, void* stream, const void* overlaps, int dtype, int n, double fg_thresh, double bg_hi,
+                    double bg_lo, int32_t* fg_list, int32_t* bg_list, int32_t* counts) {
+  MXR_REQUIRE(hh != nullptr && counts != nullptr, MXR_ERR_INVALID, "mxr_fg_bg_lists: NULL argument");
+  MXR_REQUIRE(n >= 0 && (n == 0 || (overlaps && fg_list && bg_list)), MXR_ERR_INVALID, "mxr_fg_bg_lists: bad arrays");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  h->last_launches = 0;
+  prof_begin(h, s, ST_PROPOSAL_TARGET);
+  if (dtype == MXR_DTYPE_F64)
+    fg_bg_lists_kernel<double><<<1, 1024, 0, s>>>((const double*)overlaps, n, fg_thresh, bg_hi, bg_lo, fg_list, bg_list, counts);
+  else if (dtype == MXR_DTYPE_F32)
+    fg_bg_lists_kernel<float><<<1, 1024, 0, s>>>((const float*)overlaps, n, (float)fg_thresh, (float)bg_hi, (float)bg_lo, fg_list,
+                                                 bg_list, counts);
+  else {
+    set_error("mxr_fg_bg_lists: dtype must be f32 or f64");
+    return MXR_ERR_INVALID;
+  }
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+int mxr_fg_bg_lists_host(mxr_handle_t hh, const void* overlaps, int dtype, int n, double fg_thresh, double bg_hi, double bg_lo,
+                         int32_t* fg_list, int32_t* bg_list, int32_t* counts) {
+  MXR_REQUIRE(hh != nullptr && counts != nullptr && n >= 0, MXR_ERR_INVALID, "mxr_fg_bg_lists_host: bad argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  const size_t es = dtype == MXR_DTYPE_F64 ? 8 : 4;
+  Carver c(nullptr);
+  c.take<char>((size_t)n * es + 8);
+  c.take<int>(n + 1);
+  c.take<int>(n + 1);
+  c.take<int>(2);
+  MXR_TRY(ensure_device_ws(h, align_up(c.off, 256)));
+  Carver d(h->d_ws);
+  char* d_ov = d.take<char>((size_t)n * es + 8);
+  int* d_fg = d.take<int>(n + 1);
+  int* d_bg = d.take<int>(n + 1);
+  int* d_cnt = d.take<int>(2);
+  cudaStream_t s = h->stream;
+  if (n) MXR_CUDA(cudaMemcpyAsync(d_ov, overlaps, (size_t)n * es, cudaMemcpyHostToDevice, s));
+  MXR_TRY(mxr_fg_bg_lists(hh, s, d_ov, dtype, n, fg_thresh, bg_hi, bg_lo, d_fg, d_bg, d_cnt));
+  if (n) {
+    MXR_CUDA(cudaMemcpyAsync(fg_list, d_fg, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpyAsync(bg_list, d_bg, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+  }
+  MXR_CUDA(cudaMemcpyAsync(counts, d_cnt, 8, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaStreamSynchronize(s));
+  return MXR_OK;
+}
+
+// ---- proposal-target gather --------------------------------------------------------------
+static int pt_args(const mxr_proposal_target_params* p, PtGather* a) {
+  MXR_REQUIRE(p != nullptr, MXR_ERR_INVALID, "proposal_target: NULL params");
+  MXR_REQUIRE(p->num_rois >= 1 && p->num_gt >= 1 && p->num_keep >= 0 && p->num_classes >= 1 && p->fg_this >= 0,
+              MXR_ERR_INVALID, "proposal_target: bad sizes R=%d G=%d K=%d C=%d", p->num_rois, p->num_gt, p->num_keep,
+              p->num_classes);
+  a->K = p->num_keep;
+  a->fg_this = p->fg_this;
+  a->num_classes = p->num_classes;
+  a->normalize = p->normalize;
+  for (int i = 0; i < 4; ++i) {
+    a->mean[i] = p->means[i];
+    a->stdv[i] = p->stds[i];
+    a->inside_w[i] = p->inside_weights[i];
+  }
+  return MXR_OK;
+}
+
+int mxr_proposal_target_gather(mxr_handle_t hh, void* stream, const mxr_proposal_target_params* p, const float* rois,
+                               const float* gt_boxes, const int32_t* gt_assignment, const int32_t* keep_inds,
+                               float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_target_gather: NULL handle");
+  PtGather a;
+  MXR_TRY(pt_args(p, &a));
+  if (a.K == 0) return MXR_OK;
+  MXR_REQUIRE(rois && gt_boxes && gt_assignment && keep_inds && out_rois && labels && bbox_targets && inside && outside,
+              MXR_ERR_INVALID, "mxr_proposal_target_gather: NULL array");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  a.rois = rois;
+  a.gt = gt_boxes;
+  a.assignment = gt_assignment;
+  a.keep = keep_inds;
+  a.out_rois = out_rois;
+  a.labels = labels;
+  a.targets = bbox_targets;
+  a.inside = inside;
+  a.outside = outside;
+  const long long total = (long long)a.K * a.num_classes;
+  h->last_launches = 0;
+  prof_begin(h, s, ST_PROPOSAL_TARGET);
+  proposal_target_gather_kernel<<<(int)((total + 255) / 256), 256, 0, s>>>(a);
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+int mxr_proposal_target_gather_host(mxr_handle_t hh, const mxr_proposal_target_params* p, const float* rois,
+                                    const float* gt_boxes, const int32_t* gt_assignment, const int32_t* keep_inds,
+                                    float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside) {
+  MXR_REQUIRE(hh != nullptr && p != nullptr, MXR_ERR_INVALID, "mxr_proposal_target_gather_host: NULL argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  const size_t R = p->num_rois, G = p->num_gt, K = p->num_keep, C4 = 4 * (size_t)p->num_classes;
+  if (K == 0) return MXR_OK;
+  for (int pass = 0; pass < 2; ++pass) {
+    Carver c(pass ? h->d_ws : nullptr);
+    float* d_rois = c.take<float>(R * 5);
+    float* d_gt = c.take<float>(G * 5);
+    int* d_as = c.take<int>(R);
+    int* d_keep = c.take<int>(K);
+    float* d_or = c.take<float>(K * 5);
+    float* d_lab = c.take<float>(K);
+    float* d_t = c.take<float>(K * C4);
+    float* d_i = c.take<float>(K * C4);
+    float* d_o = c.take<float>(K * C4);
+    if (!pass) {
+      MXR_TRY(ensure_device_ws(h, align_up(c.off, 256)));
+      continue;
+    }
+    cudaStream_t s = h->stream;
+    MXR_CUDA(cudaMemcpyAsync(d_rois, rois, R * 5 * 4, cudaMemcpyHostToDevice, s));
+    MXR_CUDA(cudaMemcpyAsync(d_gt, gt_boxes, G * 5 * 4, cudaMemcpyHostToDevice, s));
+    MXR_CUDA(cudaMemcpyAsync(d_as, gt_assignment, R * 4, cudaMemcpyHostToDevice, s));
+    MXR_CUDA(cudaMemcpyAsync(d_keep, keep_inds, K * 4, cudaMemcpyHostToDevice, s));
+    MXR_TRY(mxr_proposal_target_gather(hh, s, p, d_rois, d_gt, d_as, d_keep, d_or, d_lab, d_t, d_i, d_o));
+    MXR_CUDA(cudaMemcpyAsync(out_rois, d_or, K * 5 * 4, cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpyAsync(labels, d_lab, K * 4, cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpyAsync(bbox_targets, d_t, K * C4 * 4, cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpyAsync(inside, d_i, K * C4 * 4, cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpyAsync(outside, d_o, K * C4 * 4, cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaStreamSynchronize(s));
+  }
+  return MXR_OK;
+}
+
+}  // extern "C"

@@ -20,25 +20,27 @@ def _float_array(a):
 
 def bbox_transform(ex_rois, gt_rois):
     """Regression targets from ex_rois to gt_rois, (N,4) each (reference: bbox_transform.py:8-32).
-    Result dtype is the promoted dtype of the inputs (float32 only when both are float32)."""
+    Like numpy, each side is evaluated in its own dtype and the result in the promoted one
+    (float32 only when both inputs are float32)."""
     lib, h = _lib.load(), _lib.default_handle()
     if _lib.is_device_array(ex_rois):
         import torch
-        dt = torch.float32 if (ex_rois.dtype == torch.float32 and gt_rois.dtype == torch.float32) else torch.float64
-        ex = ex_rois[:, :4].to(dt).contiguous()
-        gt = gt_rois[:, :4].to(dt).contiguous()
+        ex = (ex_rois if ex_rois.dtype in (torch.float32, torch.float64) else ex_rois.double())[:, :4].contiguous()
+        gt = (gt_rois if gt_rois.dtype in (torch.float32, torch.float64) else gt_rois.double())[:, :4].contiguous()
+        dt = torch.float32 if (ex.dtype == torch.float32 and gt.dtype == torch.float32) else torch.float64
         out = torch.empty((ex.shape[0], 4), dtype=dt, device=ex.device)
-        _lib.check(lib.mxr_bbox_transform(h.ptr, _lib.current_stream_ptr(ex), ex.data_ptr(), gt.data_ptr(),
-                                          0 if dt == torch.float32 else 1, ex.shape[0], out.data_ptr()))
+        _lib.check(lib.mxr_bbox_transform(h.ptr, _lib.current_stream_ptr(ex), ex.data_ptr(),
+                                          0 if ex.dtype == torch.float32 else 1, gt.data_ptr(),
+                                          0 if gt.dtype == torch.float32 else 1, ex.shape[0], out.data_ptr()))
         return out
-    ex, gt = np.asarray(ex_rois), np.asarray(gt_rois)
-    dt = np.float32 if (ex.dtype == np.float32 and gt.dtype == np.float32) else np.float64
-    ex = np.ascontiguousarray(ex[:, :4], dtype=dt)
-    gt = np.ascontiguousarray(gt[:, :4], dtype=dt)
+    ex = _float_array(np.asarray(ex_rois)[:, :4])
+    gt = _float_array(np.asarray(gt_rois)[:, :4])
     if ex.shape[0] != gt.shape[0]:
         raise ValueError("bbox_transform: %d ex_rois vs %d gt_rois" % (ex.shape[0], gt.shape[0]))
+    dt = np.float32 if (ex.dtype == np.float32 and gt.dtype == np.float32) else np.float64
     out = np.empty((ex.shape[0], 4), dtype=dt)
-    _lib.check(lib.mxr_bbox_transform_host(h.ptr, _lib.hptr(ex), _lib.hptr(gt), _code(dt), ex.shape[0], _lib.hptr(out)))
+    _lib.check(lib.mxr_bbox_transform_host(h.ptr, _lib.hptr(ex), _code(ex.dtype), _lib.hptr(gt), _code(gt.dtype),
+                                           ex.shape[0], _lib.hptr(out)))
     return out
 
 

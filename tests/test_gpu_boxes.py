@@ -78,8 +78,11 @@ def test_bbox_transform_vs_reference_fixture():
     assert t32.dtype == np.float32
     assert np.array_equal(t32[:, :2], h["bt_f32"][:, :2])
     np.testing.assert_allclose(t32[:, 2:], h["bt_f32"][:, 2:], rtol=2e-6, atol=1e-7)
-    mixed = bbox_transform(rois.astype(np.float64), g)             # promotes to float64
-    assert mixed.dtype == np.float64 and np.array_equal(mixed[:, :2], h["bt_f64"][:, :2])
+    # mixed dtypes (rcnn/minibatch.py:338: float64 anchors, float32 gt): each side in its own dtype first
+    for e, q in ((rois.astype(np.float64), g), (rois, g.astype(np.float64))):
+        mixed, want = bbox_transform(e, q), restate.bbox_transform(e, q)
+        assert mixed.dtype == np.float64 and np.array_equal(mixed[:, :2], want[:, :2])
+        np.testing.assert_allclose(mixed[:, 2:], want[:, 2:], rtol=1e-13, atol=1e-15)
 
 
 def test_bbox_overlaps_bit_exact():
