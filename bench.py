@@ -197,6 +197,8 @@ def algorithmic_bytes(cfg, B):
         "decode_filter_kernel": B * (24 * N + 12),
         # select+sort+gather: reads keys 4N, gathers 5 floats per selected box, writes box/area/score/index (48 B)
         "topk_sort_kernel": B * (4 * N + 68 * k),
+        # fused kernel = the whole op: its algorithmic bytes are the op's mandatory I/O
+        "proposal_cluster_kernel": B * (20 * N + 12 + 24 * post),
     }
 
 
@@ -340,9 +342,10 @@ def run_gpu_arm(args, rank, world, local_rank):
     # ---- final all-gather of the per-image outputs (harness only; not in the timed path) ----
     checksum = None
     if dist is not None:
-        gathered = [torch.empty_like(keep) for _ in range(world)]
-        dist.all_gather(gathered, keep)
-        checksum = int(sum(int(g.sum().item()) for g in gathered))
+        from mxrcnn_b200 import shard
+        # rank r owns global images r, r+world, ...: gather the keep lists of the last global batch
+        full = shard.all_gather_outputs(keep, world * B)
+        checksum = shard.checksum(full.cpu().numpy())
 
     if rank == 0:
         peak, peak_src = measured_peaks()

@@ -70,6 +70,8 @@ int mxr_create(int device, mxr_handle_t* out) {
   h->device = device;
   MXR_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   MXR_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
+  const char* nc = getenv("MXRCNN_B200_NO_CLUSTER");
+  h->no_cluster = (nc && nc[0] == '1') ? 1 : 0;
   *out = reinterpret_cast<mxr_handle_t>(h);
   return MXR_OK;
 }
@@ -139,7 +141,8 @@ int mxr_profile_read(mxr_handle_t hh, int max_stages, double* total_ms, int32_t*
 const char* mxr_profile_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"memset",          "decode_filter_kernel", "topk_sort_kernel", "nms_stripe_kernel",
                                         "nms_scan_kernel", "nms_prepare_kernel",   "boxes_kernels",    "overlaps_kernels",
-                                        "anchor_target_kernels", "proposal_target_kernels", "nms_coop_kernel"};
+                                        "anchor_target_kernels", "proposal_target_kernels", "nms_coop_kernel",
+                                        "proposal_cluster_kernel"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 

@@ -67,7 +67,8 @@ enum Stage {
   ST_ANCHOR_TARGET = 8,
   ST_PROPOSAL_TARGET = 9,
   ST_NMS_COOP = 10,
-  ST_COUNT = 11
+  ST_CLUSTER = 11,
+  ST_COUNT = 12
 };
 
 struct ProfRec {
@@ -91,6 +92,7 @@ struct Handle {
   int smem_attr[8];   // largest dynamic-smem opt-in already set per kernel (0 topk, 1 prep f32, 2 prep f64, 3.. coop)
   int coop_grid[4];   // co-resident grid size of the cooperative kernels (0: not queried yet)
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
+  int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
 };
 
 // Bracket one kernel launch.  No-ops unless mxr_profile_enable(h, 1) was called.

@@ -114,7 +114,7 @@ template <typename T>
 __device__ __forceinline__ void coop_tile_task(const CoopArgs<T>& g, int b, int u, int c0, typename Ar<T>::Box* s_box,
                                                T* s_area) {
   const Ctrl c = ld_ctrl(g.ctrl + b);
-  if (c.done || c0 >= c.n) return;
+  if (c.done || c0 >= c.n || c0 < c.pad[0] * kCoopW) return;  // pad[0]: first stripe still to walk
   const int lane = threadIdx.x & 31;
   const int c1 = min(c0 + kCoopW, c.n);
   const typename Ar<T>::Box* box = g.a.box + (size_t)b * g.a.cap;
@@ -170,7 +170,7 @@ __device__ __forceinline__ void coop_scan(const CoopArgs<T>& g, int b, int c0, u
                                           int* s_finish) {
   Ctrl* cb = g.ctrl + b;
   const Ctrl cv = ld_ctrl(cb);
-  if (cv.done) return;
+  if (cv.done || c0 < cv.pad[0] * kCoopW) return;
   const int n = cv.n;
   const int tid = threadIdx.x;
   int nk = cv.nkept;
@@ -272,16 +272,30 @@ __global__ void __launch_bounds__(1024, 1) nms_coop_kernel(CoopArgs<T> g, Tier2 
   const int warp = threadIdx.x >> 5;
   const int n64 = (max(g.n_max, 1) + 63) & ~63;
   const int nstripes = (n64 + kCoopW - 1) / kCoopW;
+  if (g.tier2_at == -2) {
+    // tail of the fused cluster kernel: whatever is not done needs the full candidate order first
+    int remaining = 0;
+    for (int b = threadIdx.x; b < g.B; b += blockDim.x) remaining |= ld_ctrl(g.ctrl + b).done ? 0 : 1;
+    if (!__syncthreads_or(remaining)) return;  // the usual case: nothing left, no grid barrier needed
+    for (int b = blockIdx.x; b < g.B; b += gridDim.x) {
+      if (!ld_ctrl(g.ctrl + b).done && t2.wanted(b)) t2.run(b, g.ctrl, coop_smem, s_st, &s_cnt);
+      __syncthreads();
+    }
+    grid.sync();
+  }
   for (int s = 0; s < nstripes; ++s) {
     const int c0 = s * kCoopW;
     // anything left to do?  (ctrl is stable here: written before the previous grid.sync / kernel boundary)
-    int active = 0;
+    int active = 0, remaining = 0;
     for (int b = threadIdx.x; b < g.B; b += blockDim.x) {
       const Ctrl c = ld_ctrl(g.ctrl + b);
-      active |= (!c.done && (c0 < c.n || s == 0)) ? 1 : 0;
+      remaining |= c.done ? 0 : 1;
+      active |= (!c.done && s >= c.pad[0] && (c0 < c.n || s == 0)) ? 1 : 0;
     }
+    remaining = __syncthreads_or(remaining);
     active = __syncthreads_or(active);
-    if (!active) break;
+    if (!remaining) break;
+    if (!active) continue;  // e.g. every remaining problem resumes at a later stripe
     if (s == g.tier2_at) {
       for (int b = blockIdx.x; b < g.B; b += gridDim.x) {
         if (!ld_ctrl(g.ctrl + b).done && t2.wanted(b)) t2.run(b, g.ctrl, coop_smem, s_st, &s_cnt);

@@ -3,6 +3,7 @@
 
 #include "nms_coop.cuh"
 #include "nms_host.cuh"
+#include "proposal_cluster.cuh"
 #include "proposal_kernels.cuh"
 
 using namespace mxr;
@@ -137,11 +138,18 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   pg.cls_fg_offset = cls_fg_offset;
   h->last_launches = 0;
   MXR_CUDA(cudaMemsetAsync(L.ctrl, 0, L.zero_bytes, s));
-  const int n_threads = L.n_crop > L.n_full ? L.n_crop : L.n_full;
-  dim3 g1((n_threads + 255) / 256, L.B);
-  prof_begin(h, s, ST_DECODE);
-  decode_filter_kernel<<<g1, 256, 0, s>>>(pg, at, cls_prob, bbox_pred, im_info, p->min_size, L.keys, L.ctrl);
-  prof_end(h, s);
+  // Fast path: the fused cluster kernel (one launch, one 8-CTA cluster per image).  It needs an
+  // image's anchors to fit 8 CTAs x 12 keys x 1024 threads; MXRCNN_B200_NO_CLUSTER=1 forces the
+  // multi-kernel path (used by the tests to cover both).
+  const int cluster_items = (L.n_crop + kClusterSize * 1024 - 1) / (kClusterSize * 1024);
+  const bool use_cluster = cluster_items <= 12 && !h->no_cluster;
+  if (!use_cluster) {
+    const int n_threads = L.n_crop > L.n_full ? L.n_crop : L.n_full;
+    dim3 g1((n_threads + 255) / 256, L.B);
+    prof_begin(h, s, ST_DECODE);
+    decode_filter_kernel<<<g1, 256, 0, s>>>(pg, at, cls_prob, bbox_pred, im_info, p->min_size, L.keys, L.ctrl);
+    prof_end(h, s);
+  }
   TopkCall tc;
   tc.pg = pg;
   tc.ta.keys = L.keys;
@@ -161,13 +169,15 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   size_t smem1 = (size_t)head_pow2 * 8;
   if (smem1 < 32 * 256 * sizeof(u32)) smem1 = 32 * 256 * sizeof(u32);
   tc.smem_pairs = (int)(smem1 / 8);
-  prof_begin(h, s, ST_TOPK);
-  if (L.n_crop <= 24 * 1024) {
-    topk_kernel<24><<<L.B, 1024, smem1, s>>>(tc, at, L.head, 0, L.ctrl);
-  } else {
-    topk_kernel<0><<<L.B, 1024, smem1, s>>>(tc, at, L.head, 0, L.ctrl);
+  if (!use_cluster) {
+    prof_begin(h, s, ST_TOPK);
+    if (L.n_crop <= 24 * 1024) {
+      topk_kernel<24><<<L.B, 1024, smem1, s>>>(tc, at, L.head, 0, L.ctrl);
+    } else {
+      topk_kernel<0><<<L.B, 1024, smem1, s>>>(tc, at, L.head, 0, L.ctrl);
+    }
+    prof_end(h, s);
   }
-  prof_end(h, s);
   // ---- NMS: one cooperative kernel; its deferred phase sorts the rest if an image needs it ----
   CoopArgs<double> ca;
   ca.ctrl = L.ctrl;
@@ -195,12 +205,53 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   ca.max_keep = p->post_nms_top_n > 0 ? L.keep_cap : 0;
   ca.tier2_at = (L.head < L.n_max) ? L.head / kCoopW : -1;
   ca.thr = p->nms_thresh;
+  if (use_cluster) {
+    ClusterArgs cl;
+    cl.pg = pg;
+    cl.at = at;
+    cl.cls_prob = cls_prob;
+    cl.bbox_pred = bbox_pred;
+    cl.im_info = im_info;
+    cl.min_size = p->min_size;
+    cl.pre_nms = p->pre_nms_top_n;
+    cl.head = L.head;
+    cl.max_keep = ca.max_keep;
+    cl.thr = p->nms_thresh;
+    cl.keys = L.keys;
+    cl.a = ca.a;
+    cl.o = ca.o;
+    cl.ctrl = L.ctrl;
+    const size_t smem_c = cluster_smem_bytes();
+    void (*kern)(ClusterArgs) = cluster_items <= 4 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
+    const int slot = cluster_items <= 4 ? 4 : 5;
+    if ((int)smem_c > h->smem_attr[slot]) {
+      MXR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
+      h->smem_attr[slot] = (int)smem_c;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(L.B * kClusterSize);
+    cfg.blockDim = dim3(1024);
+    cfg.dynamicSmemBytes = smem_c;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kClusterSize;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    prof_begin(h, s, ST_CLUSTER);
+    MXR_CUDA(cudaLaunchKernelEx(&cfg, kern, cl));
+    prof_end(h, s);
+    ca.tier2_at = -2;  // the general kernel below only picks up what the cluster kernel left undone
+  }
   ProposalTier2 t2;
   t2.tc = tc;
   t2.at = at;
   t2.head = L.head;
   size_t tier2_smem = 0;
-  if (ca.tier2_at >= 0) tier2_smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 8 : 32 * 256 * sizeof(u32);
+  if (ca.tier2_at != -1) tier2_smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 8 : 32 * 256 * sizeof(u32);
   const size_t smem2 = coop_smem_bytes(sizeof(double4), sizeof(double), tier2_smem);
   t2.tc.smem_pairs = L.use_smem_sort ? (int)(smem2 / 8) : 0;
   if (h->coop_grid[0] == 0 || (int)smem2 > h->smem_attr[3]) {

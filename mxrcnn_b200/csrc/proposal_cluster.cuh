@@ -1,0 +1,469 @@
+// Fused RPN proposal kernel: ONE launch, one thread-block cluster (8 CTAs x 1024 threads) per image.
+//
+// rcnn/rpn/proposal.py:39-149 end to end inside the cluster, phases separated by cluster barriers
+// (~0.2 us) instead of kernel boundaries, with distributed shared memory as the exchange medium:
+//   P1 decode + clip + min-size filter (each CTA an eighth of the anchors, keys stay in registers)
+//   P2 radix select of the head of the candidate order: per-CTA digit histograms are summed into
+//      the leader CTA's shared memory with DSMEM atomics, every CTA reads the sum back
+//   P3 the selected composites are written straight into the leader's sort buffer (DSMEM stores)
+//   P4 the leader sorts the head (<= 4096 boxes)          P5 all CTAs re-decode the head boxes
+//   P6 per 1024-box stripe: the other CTAs evaluate the IoU bit tiles and store them directly into
+//      the leader's shared bit matrix (DSMEM), the leader walks the stripe greedily
+//   P7 the leader writes rois / scores / keep lists.
+// Anything the head cannot settle (post-NMS quota not reached within the head, score ties cut by
+// the head boundary) is left, with its state in global memory, to the general cooperative kernel
+// (nms_coop.cuh), which is launched right after and returns at once when nothing is left.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "nms_coop.cuh"
+#include "proposal_kernels.cuh"
+
+namespace mxr {
+
+static const int kClusterSize = 8;
+
+struct ClusterArgs {
+  ProposalGeom pg;
+  AnchorTable at;
+  const float* cls_prob;
+  const float* bbox_pred;
+  const float* im_info;
+  float min_size;
+  int pre_nms;
+  int head;          // sorted prefix handled here (multiple of 64, <= 4096)
+  int max_keep;      // > 0: post_nms_top_n
+  double thr;
+  u32* keys;         // [b][n_crop] global copy of the keys for the deferred full sort
+  NmsArrays<double> a;
+  NmsOutputs o;
+  Ctrl* ctrl;
+};
+
+__device__ __forceinline__ double4 ldcg_box(const double4* p) {
+  const double2 a = __ldcg(reinterpret_cast<const double2*>(p));
+  const double2 b = __ldcg(reinterpret_cast<const double2*>(p) + 1);
+  return make_double4(a.x, a.y, b.x, b.y);
+}
+
+__device__ __forceinline__ void remote_or64(u64* p, u64 v) {
+  u32* q = reinterpret_cast<u32*>(p);
+  const u32 lo = (u32)v, hi = (u32)(v >> 32);
+  if (lo) atomicOr(q, lo);
+  if (hi) atomicOr(q + 1, hi);
+}
+
+// Greedy walk of one stripe whose bit rows already sit in shared memory (pitch kCoopPitch).
+// Whole CTA.  Returns the new kept count; *fin_out != 0 when the quota was reached.
+__device__ __forceinline__ int scan_rows_smem(const u64* sM, u64* s_removed, int rows, int c0, int nk, int max_keep,
+                                              int* kept_slot, u64* s_keptbits, int* s_finish, int* fin_out) {
+  const int tid = threadIdx.x;
+  const int nblk = (rows + 63) >> 6;
+  int finished = 0;
+  for (int blk = 0; blk < nblk; ++blk) {
+    __syncthreads();
+    if (tid < 32) {
+      const u64 word0 = s_removed[blk];
+      const int nvalid = min(64, rows - blk * 64);
+      const u64 valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1ull);
+      const u64 d0 = (blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * kCoopPitch + blk] : 0ull;
+      const u64 d1 = (blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * kCoopPitch + blk] : 0ull;
+      u32 lo = (u32)(word0 | ~valid), hi = (u32)((word0 | ~valid) >> 32);
+      const u32 d0lo = (u32)d0, d0hi = (u32)(d0 >> 32), d1hi = (u32)(d1 >> 32);
+#pragma unroll
+      for (int t = 0; t < 32; ++t) {
+        const u32 rlo = __shfl_sync(0xffffffffu, d0lo, t);
+        const u32 rhi = __shfl_sync(0xffffffffu, d0hi, t);
+        if (!((lo >> t) & 1u)) {
+          lo |= rlo;
+          hi |= rhi;
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 32; ++t) {
+        const u32 rhi = __shfl_sync(0xffffffffu, d1hi, t);
+        if (!((hi >> t) & 1u)) hi |= rhi;
+      }
+      u64 kept = ~(((u64)hi << 32) | lo) & valid;
+      int fin = 0;
+      if (max_keep > 0 && nk + __popcll(kept) >= max_keep) {
+        int want = max_keep - nk;
+        u64 k2 = 0, rest = kept;
+        while (want > 0 && rest) {
+          const u64 low = rest & (~rest + 1ull);
+          k2 |= low;
+          rest ^= low;
+          --want;
+        }
+        kept = k2;
+        fin = 1;
+      }
+      if (tid == 0) {
+        *s_keptbits = kept;
+        *s_finish = fin;
+      }
+    }
+    __syncthreads();
+    const u64 kept = *s_keptbits;
+    const int fin = *s_finish;
+    if (tid < 64 && ((kept >> tid) & 1ull)) kept_slot[nk + __popcll(kept & ((1ull << tid) - 1ull))] = c0 + blk * 64 + tid;
+    nk += __popcll(kept);
+    if (fin) {
+      finished = 1;
+      break;
+    }
+    const int nw = nblk - blk - 1;
+    const int w = tid >> 6, row = tid & 63;
+    if (w < nw) {
+      const u64 v = ((kept >> row) & 1ull) ? sM[(blk * 64 + row) * kCoopPitch + blk + 1 + w] : 0ull;
+      const u32 vlo = __reduce_or_sync(0xffffffffu, (u32)v);
+      const u32 vhi = __reduce_or_sync(0xffffffffu, (u32)(v >> 32));
+      if ((tid & 31) == 0 && (vlo | vhi)) atomicOr(&s_removed[blk + 1 + w], ((u64)vhi << 32) | vlo);
+    }
+  }
+  __syncthreads();
+  *fin_out = finished;
+  return nk;
+}
+
+// grid B * kClusterSize CTAs, cluster (kClusterSize,1,1), block 1024.
+// ITEMS: keys per thread; the image's A*hc*wc anchors must fit kClusterSize*ITEMS*1024.
+template <int ITEMS>
+__global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g) {
+  namespace cgx = cooperative_groups;
+  extern __shared__ __align__(16) unsigned char dyn_smem[];
+  __shared__ u32 s_hist[256];
+  __shared__ u32 s_ghist[4][256];   // leader: cluster-wide digit histograms, one per pass
+  __shared__ int s_cnt[4];          // leader: n_valid, nan
+  __shared__ int s_sel[kClusterSize];  // leader: selected count of each CTA
+  __shared__ int s_status[2];       // leader: kept so far, quota reached
+  __shared__ u32 s_st[4];
+  __shared__ int s_local[4];
+  __shared__ u64 s_keptbits;
+  __shared__ int s_finish;
+  cgx::cluster_group cluster = cgx::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int b = blockIdx.x / kClusterSize;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const ProposalGeom& pg = g.pg;
+  const DecodeGeom& dg = pg.g;
+  // leader-resident structures, addressed through distributed shared memory
+  u64* sM = reinterpret_cast<u64*>(dyn_smem);                 // leader: [1024][17] bit rows; first the sort buffer
+  u64* s_removed = sM + kCoopW * kCoopPitch;                   // leader: [16]
+  u64* L_sM = cluster.map_shared_rank(sM, 0);
+  u64* L_removed = cluster.map_shared_rank(s_removed, 0);
+  u32* L_ghist = cluster.map_shared_rank(&s_ghist[0][0], 0);
+  int* L_cnt = cluster.map_shared_rank(s_cnt, 0);
+  int* L_sel = cluster.map_shared_rank(s_sel, 0);
+  int* L_status = cluster.map_shared_rank(s_status, 0);
+  if (rank == 0) {
+    for (int i = tid; i < 4 * 256; i += blockDim.x) (&s_ghist[0][0])[i] = 0;
+    if (tid < 4) s_cnt[tid] = 0;
+    if (tid < kCoopSW) s_removed[tid] = 0ull;
+    if (tid < 2) s_status[tid] = 0;
+  }
+  if (tid < 4) s_local[tid] = 0;
+  cluster.sync();
+
+  // ---- P1: decode + clip + min-size filter (proposal.py:77-120); keys stay in registers ----
+  const int hwc = dg.hc * dg.wc;
+  const size_t hw = (size_t)dg.H * dg.W;
+  const float* fg = g.cls_prob + (size_t)b * pg.cls_img_stride + pg.cls_fg_offset;
+  const float* deltas = g.bbox_pred + (size_t)b * 4 * dg.A * hw;
+  const float im_h = __ldg(g.im_info + b * 3), im_w = __ldg(g.im_info + b * 3 + 1), im_s = __ldg(g.im_info + b * 3 + 2);
+  const int chunk = (pg.n_crop + kClusterSize - 1) / kClusterSize;
+  const int q_begin = rank * chunk;
+  const int q_end = min(q_begin + chunk, pg.n_crop);
+  u32 rk[ITEMS];
+  {
+    int nvalid = 0, nnan = 0;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int q = q_begin + tid + i * 1024;
+      u32 key = 0;
+      bool nan = false;
+      if (q < q_end) {
+        const int a = q / hwc, r = q - a * hwc;
+        const int h = r / dg.wc, w = r - h * dg.wc;
+        double bx[4];
+        bool dnan;
+        decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx, &dnan);
+        float s;
+        if (!pg.cropped) {
+          s = __ldg(fg + (size_t)a * hw + (size_t)h * dg.W + w);
+        } else {  // quirk Q1: scores are read at the flat (H,W,A) index of the UNCROPPED map
+          const int p = r * dg.A + a;
+          const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
+          s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
+        }
+        const bool valid = passes_min_size(bx, g.min_size, im_s);
+        nan = (s != s) || dnan;
+        key = valid ? score_key32(s) : 0u;
+        g.keys[(size_t)b * pg.n_crop + q] = key;
+      }
+      rk[i] = key;
+      nvalid += __popc(__ballot_sync(0xffffffffu, key != 0u));
+      nnan += __popc(__ballot_sync(0xffffffffu, nan));
+    }
+    if (pg.cropped) {  // proposal.py:58-62 checks the whole arrays, cropped or not
+      const int fchunk = (pg.n_full + kClusterSize - 1) / kClusterSize;
+      for (int q = rank * fchunk + tid; q < min((rank + 1) * fchunk, pg.n_full); q += 1024) {
+        const float v0 = __ldg(fg + q), v1 = __ldg(deltas + q), v2 = __ldg(deltas + q + pg.n_full);
+        const float v3 = __ldg(deltas + q + 2 * (size_t)pg.n_full), v4 = __ldg(deltas + q + 3 * (size_t)pg.n_full);
+        if ((v0 != v0) || (v1 != v1) || (v2 != v2) || (v3 != v3) || (v4 != v4)) nnan = 1;
+      }
+      nnan = __popc(__ballot_sync(0xffffffffu, nnan != 0));
+    }
+    if (lane == 0) {
+      if (nvalid) atomicAdd(&s_local[0], nvalid);
+      if (nnan) atomicAdd(&s_local[1], nnan);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (s_local[0]) atomicAdd(L_cnt, s_local[0]);
+      if (s_local[1]) atomicAdd(L_cnt + 1, s_local[1]);
+    }
+  }
+  cluster.sync();
+  if (tid == 0) {
+    s_local[2] = L_cnt[0];
+    s_local[3] = L_cnt[1];
+  }
+  __syncthreads();
+  const int n_valid = s_local[2];
+  const int nan_flag = s_local[3] ? 1 : 0;
+  const int k = (g.pre_nms > 0) ? min(g.pre_nms, n_valid) : n_valid;  // proposal.py:124-125
+  const int k1 = min(g.head, k);
+
+  // ---- P2: radix select of the head threshold on the 32-bit score keys ----
+  bool bail = false;   // a run of equal scores is cut by the head boundary: leave it to the general path
+  u32 T = 1u;
+  if (k1 > 0 && k1 < n_valid) {
+    u32 prefix = 0;
+    int k_rem = k1;
+    u32 cnt = 0;
+    for (int pass = 0; pass < 4; ++pass) {
+      const int shift = 24 - 8 * pass;
+      if (tid < 256) s_hist[tid] = 0;
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        const u32 key = rk[i];
+        bool valid = key != 0u;
+        if (valid && pass > 0) valid = ((key ^ prefix) >> (shift + 8)) == 0u;
+        const u32 digit = (key >> shift) & 255u;
+        const u32 active = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+          const u32 peers = __match_any_sync(active, digit);
+          if (lane == __ffs(peers) - 1) atomicAdd(&s_hist[digit], (u32)__popc(peers));
+        }
+      }
+      __syncthreads();
+      if (tid < 256 && s_hist[tid]) atomicAdd(L_ghist + pass * 256 + tid, s_hist[tid]);
+      cluster.sync();
+      if (tid < 256) s_hist[tid] = L_ghist[pass * 256 + tid];
+      __syncthreads();
+      if (warp == 0) {
+        u32 mine = 0;
+        for (int j = 0; j < 8; ++j) mine += s_hist[255 - 8 * lane - j];
+        u32 incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+          const u32 v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const u32 excl = incl - mine;
+        if ((excl < (u32)k_rem) && ((u32)k_rem <= incl)) {
+          u32 cum = excl;
+          for (int j = 0; j < 8; ++j) {
+            const int d = 255 - 8 * lane - j;
+            const u32 c = s_hist[d];
+            if (cum + c >= (u32)k_rem) {
+              s_st[0] = (u32)d;
+              s_st[1] = (u32)k_rem - cum;
+              s_st[2] = c;
+              break;
+            }
+            cum += c;
+          }
+        }
+      }
+      __syncthreads();
+      prefix |= s_st[0] << shift;
+      k_rem = (int)s_st[1];
+      cnt = s_st[2];
+      __syncthreads();
+      if ((int)cnt == k_rem) break;
+    }
+    bail = ((int)cnt != k_rem);
+    T = prefix;
+  }
+
+  int nk = 0, fin = 0, stripes_done = 0;
+  if (!bail && k1 > 0) {
+    // ---- P3: selected composites go straight into the leader's sort buffer ----
+    const int n_pow2 = max(2, (int)(1u << (32 - __clz(k1 - 1))));
+    {
+      int mine = 0;
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) mine += __popc(__ballot_sync(0xffffffffu, rk[i] != 0u && rk[i] >= T));
+      if (tid < 4) s_local[tid] = 0;
+      __syncthreads();
+      if (lane == 0 && mine) atomicAdd(&s_local[0], mine);
+      __syncthreads();
+      if (tid == 0) L_sel[rank] = s_local[0];
+    }
+    cluster.sync();
+    if (tid == 0) {
+      int off = 0;
+      for (int r = 0; r < rank; ++r) off += L_sel[r];
+      s_local[1] = off;   // base of this CTA inside the sort buffer
+      s_local[0] = 0;     // running position inside this CTA
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const u32 key = rk[i];
+      const bool sel = key != 0u && key >= T;
+      const u32 m = __ballot_sync(0xffffffffu, sel);
+      int base = 0;
+      if (lane == 0 && m) base = atomicAdd(&s_local[0], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (sel) {
+        const int q = q_begin + tid + i * 1024;
+        const u32 p = (u32)q_to_p(q, hwc, dg.A);
+        L_sM[s_local[1] + base + __popc(m & ((1u << lane) - 1u))] = ((u64)key << 32) | (u32)(~p);
+      }
+    }
+    if (rank == 0)
+      for (int i = k1 + tid; i < n_pow2; i += blockDim.x) sM[i] = 0ull;
+    cluster.sync();
+    // ---- P4: the leader orders the head: (score desc, row index asc) -- see topk_body ----
+    if (rank == 0) bitonic_sort_desc_u64(sM, n_pow2);
+    cluster.sync();
+    // ---- P5: all CTAs re-decode their slice of the head into processing order ----
+    {
+      const int per = (k1 + kClusterSize - 1) / kClusterSize;
+      for (int i = rank * per + tid; i < min((rank + 1) * per, k1); i += blockDim.x) {
+        const int p = (int)(~(u32)L_sM[i]);
+        const int a = p % dg.A, r = p / dg.A;
+        const int h = r / dg.wc, w = r - h * dg.wc;
+        double bx[4];
+        decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx);
+        const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
+        const float s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
+        const size_t o = (size_t)b * g.a.cap + i;
+        const_cast<double4*>(g.a.box)[o] = make_double4(bx[0], bx[1], bx[2], bx[3]);
+        const_cast<double*>(g.a.area)[o] = box_area<double>(bx[0], bx[1], bx[2], bx[3]);
+        const_cast<float*>(g.a.score)[o] = s;
+        const_cast<int*>(g.a.orig)[o] = p;
+      }
+    }
+    __threadfence();
+    cluster.sync();
+    // ---- P6: stripes of 1024 boxes ----
+    const double4* box = g.a.box + (size_t)b * g.a.cap;
+    const double* area = g.a.area + (size_t)b * g.a.cap;
+    int* kept_slot = g.a.kept_slot + (size_t)b * g.a.keep_cap;
+    double4* t_box = reinterpret_cast<double4*>(dyn_smem) + warp * 64;                 // non-leader tile staging
+    double* t_area = reinterpret_cast<double*>(dyn_smem + 32 * 64 * sizeof(double4)) + warp * 64;
+    const int nstripes = (k1 + kCoopW - 1) / kCoopW;
+    for (int s = 0; s < nstripes && !fin; ++s) {
+      const int c0 = s * kCoopW;
+      const int c1 = min(c0 + kCoopW, k1);
+      if (rank > 0) {
+        const int prev_rows = nk;
+        const int tp = 2 * kCoopTri + kCoopSW * ((prev_rows + 31) / 32);
+        for (int u = (rank - 1) * 32 + warp; u < tp; u += (kClusterSize - 1) * 32) {
+          int cb, rb = 0, half = 0, rc = 0;
+          const bool tri = u < 2 * kCoopTri;
+          if (tri) {
+            int t = u >> 1;
+            half = u & 1;
+            while (t >= kCoopSW - rb) {
+              t -= kCoopSW - rb;
+              ++rb;
+            }
+            cb = rb + t;
+          } else {
+            const int v = u - 2 * kCoopTri;
+            cb = v % kCoopSW;
+            rc = v / kCoopSW;
+          }
+          const int col0 = c0 + cb * 64;
+          if (col0 >= c1) continue;
+          const int ncols = min(64, c1 - col0);
+          __syncwarp();
+          for (int j = lane; j < ncols; j += 32) {
+            t_box[j] = ldcg_box(box + col0 + j);
+            t_area[j] = __ldcg(area + col0 + j);
+          }
+          __syncwarp();
+          if (tri) {
+            const int rl = rb * 64 + half * 32 + lane;
+            const int row = c0 + rl;
+            if (row < c1) {
+              const u64 w = tile_word<double>(ldcg_box(box + row), __ldcg(area + row), t_box, t_area,
+                                              rb == cb ? (half * 32 + lane + 1) : 0, ncols, g.thr);
+              L_sM[rl * kCoopPitch + cb] = w;
+            }
+          } else {
+            u64 w = 0;
+            const int kidx = rc * 32 + lane;
+            if (kidx < nk) {
+              const int slot = __ldcg(kept_slot + kidx);
+              w = tile_word<double>(ldcg_box(box + slot), __ldcg(area + slot), t_box, t_area, 0, ncols, g.thr);
+            }
+            const u32 lo = __reduce_or_sync(0xffffffffu, (u32)w);
+            const u32 hi = __reduce_or_sync(0xffffffffu, (u32)(w >> 32));
+            if (lane == 0) remote_or64(L_removed + cb, ((u64)hi << 32) | lo);
+          }
+        }
+      }
+      cluster.sync();
+      if (rank == 0) {
+        int f = 0;
+        nk = scan_rows_smem(sM, s_removed, c1 - c0, c0, nk, g.max_keep, kept_slot, &s_keptbits, &s_finish, &f);
+        if (tid < kCoopSW) s_removed[tid] = 0ull;
+        if (tid == 0) {
+          s_status[0] = nk;
+          s_status[1] = f;
+        }
+        __threadfence();
+      }
+      cluster.sync();
+      if (tid == 0) {
+        s_local[2] = L_status[0];
+        s_local[3] = L_status[1];
+      }
+      __syncthreads();
+      nk = s_local[2];
+      fin = s_local[3];
+      stripes_done = s + 1;
+      __syncthreads();
+    }
+  }
+  // ---- P7: results, or hand-over state for the general path ----
+  if (rank == 0) {
+    const bool finished = !bail && (fin || k1 >= k);
+    Ctrl* cb = g.ctrl + b;
+    if (tid == 0) {
+      cb->n_valid = n_valid;
+      cb->nan_flag = nan_flag;
+      cb->n = k;
+      cb->nkept = nk;
+      cb->done = finished ? 1 : 0;
+      cb->pad[0] = bail ? 0 : stripes_done;   // first stripe the general path still has to walk
+    }
+    __syncthreads();
+    if (finished) coop_write_outputs<double>(g.a, g.o, cb, b, nk, k);
+  }
+  cluster.sync();  // nobody leaves while its shared memory may still be addressed
+}
+
+static inline size_t cluster_smem_bytes() {
+  const size_t leader = (size_t)kCoopW * kCoopPitch * 8 + kCoopSW * 8 + 64;
+  const size_t tiles = 32 * 64 * (sizeof(double4) + sizeof(double));
+  return leader > tiles ? leader : tiles;
+}
+
+}  // namespace mxr

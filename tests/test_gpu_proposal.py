@@ -153,3 +153,21 @@ def test_proposal_first_stripe_width_does_not_change_results():
     for fs in (64, 256, 4096):
         o = run(cls, box, info, cfg, first_stripe=fs)
         assert np.array_equal(o["keep"], base["keep"]) and np.array_equal(o["rois"], base["rois"])
+
+
+@pytest.mark.parametrize("cfgname,seed", [("tiny", 51), ("voc_test", 52), ("voc_train", 53), ("voc_alt", 54), ("wider", 55)])
+def test_fused_cluster_path_equals_multi_kernel_path(cfgname, seed, monkeypatch):
+    """The op has two implementations: the fused cluster kernel (default) and the multi-kernel path
+    (MXRCNN_B200_NO_CLUSTER=1; also the fallback for very large maps).  Same results, bit for bit."""
+    from mxrcnn_b200 import _lib
+    cfg = synth.CONFIGS[cfgname]
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    fused = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
+    monkeypatch.setenv("MXRCNN_B200_NO_CLUSTER", "1")
+    h = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_NO_CLUSTER")
+    multi = run(cls, box, info, cfg, rng=np.random.RandomState(seed), handle=h)
+    for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
+        assert np.array_equal(fused[k], multi[k]), k
+    h.close()
