@@ -16,8 +16,10 @@ struct Ar<double> {
   static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
   static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
   static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
-  static __device__ __forceinline__ double vmax(double a, double b) { return fmax(a, b); }
-  static __device__ __forceinline__ double vmin(double a, double b) { return fmin(a, b); }
+  // compare-select (DSETP + 2 SEL) instead of fmax/fmin, whose NaN handling costs ~10 instructions
+  // per call on sm_100; identical for the non-NaN values that reach these kernels
+  static __device__ __forceinline__ double vmax(double a, double b) { return a > b ? a : b; }
+  static __device__ __forceinline__ double vmin(double a, double b) { return a < b ? a : b; }
   // guard band of the division-free IoU test: 1 -/+ 2^-48 (rounding error of the test is < 2^-51)
   static __device__ __forceinline__ double band_lo() { return 1.0 - 3.552713678800501e-15; }
   static __device__ __forceinline__ double band_hi() { return 1.0 + 3.552713678800501e-15; }
@@ -69,6 +71,26 @@ __device__ __forceinline__ bool iou_exceeds(T ax1, T ay1, T ax2, T ay2, T aarea,
     if (inter >= A::mul(t, A::band_hi())) return true;
   }
   return !(A::div(inter, uni) <= thr);
+}
+
+// Same predicate with the loop-invariant parts hoisted: thr_lo = thr*(1-band), thr_hi = thr*(1+band)
+// (thr > 0 checked by the caller; the extra rounding of the hoisted products is < 2^-52, far inside
+// the 2^-48 band).  Returns 0 = keep, 1 = suppressed, 2 = inside the band / degenerate: the caller
+// re-evaluates with iou_exceeds().  Branch-free so that a warp does not diverge on it.
+__device__ __forceinline__ int iou_band_f64(double ax1, double ay1, double ax2, double ay2, double aarea, double bx1,
+                                            double by1, double bx2, double by2, double barea, double thr_lo,
+                                            double thr_hi) {
+  typedef Ar<double> A;
+  const double xx1 = A::vmax(ax1, bx1), yy1 = A::vmax(ay1, by1);
+  const double xx2 = A::vmin(ax2, bx2), yy2 = A::vmin(ay2, by2);
+  const double w0 = A::add(A::sub(xx2, xx1), 1.0), h0 = A::add(A::sub(yy2, yy1), 1.0);
+  const double w = w0 > 0.0 ? w0 : 0.0, h = h0 > 0.0 ? h0 : 0.0;
+  const double inter = A::mul(w, h);
+  const double uni = A::sub(A::add(aarea, barea), inter);
+  const bool pos = uni > 0.0;
+  const bool keep = inter <= A::mul(thr_lo, uni);
+  const bool supp = inter >= A::mul(thr_hi, uni);
+  return !pos ? 2 : (keep ? 0 : (supp ? 1 : 2));
 }
 
 // Order-preserving map f32 -> u32 (larger float => larger key).  -0.0 is folded onto

@@ -22,6 +22,11 @@
 namespace mxr {
 
 static const int kClusterSize = 8;
+static const int kCW = 256;        // stripe width inside the cluster kernel (cluster barriers are cheap)
+static const int kCSW = 4;         // words per stripe row
+static const int kCPitch = 5;      // shared-memory row pitch in words
+static const int kCTriTasks = 80;  // 10 upper-triangle tiles x 2 row halves x 4 column quarters
+static const int kSortMax = 4096;  // head capacity of the leader's sort buffer
 
 struct ClusterArgs {
   ProposalGeom pg;
@@ -53,9 +58,30 @@ __device__ __forceinline__ void remote_or64(u64* p, u64 v) {
   if (hi) atomicOr(q + 1, hi);
 }
 
+// 16 columns of one row: bit j set when column j is suppressed by the row box (nms.py:25-36).
+__device__ __forceinline__ u32 tile_bits16(const double4 rb, double rarea, const double4* cols, const double* careas,
+                                           int j_begin, int j_end, double thr, double thr_lo, double thr_hi) {
+  u32 bits = 0;
+  if (thr > 0.0) {
+#pragma unroll 4
+    for (int j = j_begin; j < j_end; ++j) {
+      const double4 cb = cols[j];
+      int r = iou_band_f64(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr_lo, thr_hi);
+      if (r == 2) r = iou_exceeds<double>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr) ? 1 : 0;
+      bits |= (u32)r << j;
+    }
+  } else {
+    for (int j = j_begin; j < j_end; ++j) {
+      const double4 cb = cols[j];
+      if (iou_exceeds<double>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr)) bits |= 1u << j;
+    }
+  }
+  return bits;
+}
+
 // Greedy walk of one stripe whose bit rows already sit in shared memory (pitch kCoopPitch).
 // Whole CTA.  Returns the new kept count; *fin_out != 0 when the quota was reached.
-__device__ __forceinline__ int scan_rows_smem(const u64* sM, u64* s_removed, int rows, int c0, int nk, int max_keep,
+__device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_removed, int rows, int c0, int nk, int max_keep,
                                               int* kept_slot, u64* s_keptbits, int* s_finish, int* fin_out) {
   const int tid = threadIdx.x;
   const int nblk = (rows + 63) >> 6;
@@ -66,8 +92,8 @@ __device__ __forceinline__ int scan_rows_smem(const u64* sM, u64* s_removed, int
       const u64 word0 = s_removed[blk];
       const int nvalid = min(64, rows - blk * 64);
       const u64 valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1ull);
-      const u64 d0 = (blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * kCoopPitch + blk] : 0ull;
-      const u64 d1 = (blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * kCoopPitch + blk] : 0ull;
+      const u64 d0 = (blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * pitch + blk] : 0ull;
+      const u64 d1 = (blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * pitch + blk] : 0ull;
       u32 lo = (u32)(word0 | ~valid), hi = (u32)((word0 | ~valid) >> 32);
       const u32 d0lo = (u32)d0, d0hi = (u32)(d0 >> 32), d1hi = (u32)(d1 >> 32);
 #pragma unroll
@@ -115,7 +141,7 @@ __device__ __forceinline__ int scan_rows_smem(const u64* sM, u64* s_removed, int
     const int nw = nblk - blk - 1;
     const int w = tid >> 6, row = tid & 63;
     if (w < nw) {
-      const u64 v = ((kept >> row) & 1ull) ? sM[(blk * 64 + row) * kCoopPitch + blk + 1 + w] : 0ull;
+      const u64 v = ((kept >> row) & 1ull) ? sM[(blk * 64 + row) * pitch + blk + 1 + w] : 0ull;
       const u32 vlo = __reduce_or_sync(0xffffffffu, (u32)v);
       const u32 vhi = __reduce_or_sync(0xffffffffu, (u32)(v >> 32));
       if ((tid & 31) == 0 && (vlo | vhi)) atomicOr(&s_removed[blk + 1 + w], ((u64)vhi << 32) | vlo);
@@ -148,8 +174,12 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   const ProposalGeom& pg = g.pg;
   const DecodeGeom& dg = pg.g;
   // leader-resident structures, addressed through distributed shared memory
-  u64* sM = reinterpret_cast<u64*>(dyn_smem);                 // leader: [1024][17] bit rows; first the sort buffer
-  u64* s_removed = sM + kCoopW * kCoopPitch;                   // leader: [16]
+  u64* sortbuf = reinterpret_cast<u64*>(dyn_smem);                           // leader: [kSortMax] head sort buffer
+  u64* sM = sortbuf + kSortMax;                                              // leader: [256][5] bit rows of one stripe
+  u64* s_removed = sM + kCW * kCPitch;                                       // leader: [4]
+  double4* t_box = reinterpret_cast<double4*>(s_removed + 8) + warp * 16;    // every CTA: per-warp column staging
+  double* t_area = reinterpret_cast<double*>(reinterpret_cast<double4*>(s_removed + 8) + 32 * 16) + warp * 16;
+  u64* L_sort = cluster.map_shared_rank(sortbuf, 0);
   u64* L_sM = cluster.map_shared_rank(sM, 0);
   u64* L_removed = cluster.map_shared_rank(s_removed, 0);
   u32* L_ghist = cluster.map_shared_rank(&s_ghist[0][0], 0);
@@ -159,7 +189,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   if (rank == 0) {
     for (int i = tid; i < 4 * 256; i += blockDim.x) (&s_ghist[0][0])[i] = 0;
     if (tid < 4) s_cnt[tid] = 0;
-    if (tid < kCoopSW) s_removed[tid] = 0ull;
+    if (tid < kCSW) s_removed[tid] = 0ull;
     if (tid < 2) s_status[tid] = 0;
   }
   if (tid < 4) s_local[tid] = 0;
@@ -331,20 +361,20 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       if (sel) {
         const int q = q_begin + tid + i * 1024;
         const u32 p = (u32)q_to_p(q, hwc, dg.A);
-        L_sM[s_local[1] + base + __popc(m & ((1u << lane) - 1u))] = ((u64)key << 32) | (u32)(~p);
+        L_sort[s_local[1] + base + __popc(m & ((1u << lane) - 1u))] = ((u64)key << 32) | (u32)(~p);
       }
     }
     if (rank == 0)
-      for (int i = k1 + tid; i < n_pow2; i += blockDim.x) sM[i] = 0ull;
+      for (int i = k1 + tid; i < n_pow2; i += blockDim.x) sortbuf[i] = 0ull;
     cluster.sync();
     // ---- P4: the leader orders the head: (score desc, row index asc) -- see topk_body ----
-    if (rank == 0) bitonic_sort_desc_u64(sM, n_pow2);
+    if (rank == 0) bitonic_sort_desc_u64(sortbuf, n_pow2);
     cluster.sync();
     // ---- P5: all CTAs re-decode their slice of the head into processing order ----
     {
       const int per = (k1 + kClusterSize - 1) / kClusterSize;
       for (int i = rank * per + tid; i < min((rank + 1) * per, k1); i += blockDim.x) {
-        const int p = (int)(~(u32)L_sM[i]);
+        const int p = (int)(~(u32)L_sort[i]);
         const int a = p % dg.A, r = p / dg.A;
         const int h = r / dg.wc, w = r - h * dg.wc;
         double bx[4];
@@ -360,70 +390,73 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     }
     __threadfence();
     cluster.sync();
-    // ---- P6: stripes of 1024 boxes ----
+    // ---- P6: stripes of 256 boxes (cluster barriers cost ~0.2 us, so narrow stripes keep the
+    //      evaluated IoU pairs close to what the greedy walk really needs) ----
     const double4* box = g.a.box + (size_t)b * g.a.cap;
     const double* area = g.a.area + (size_t)b * g.a.cap;
     int* kept_slot = g.a.kept_slot + (size_t)b * g.a.keep_cap;
-    double4* t_box = reinterpret_cast<double4*>(dyn_smem) + warp * 64;                 // non-leader tile staging
-    double* t_area = reinterpret_cast<double*>(dyn_smem + 32 * 64 * sizeof(double4)) + warp * 64;
-    const int nstripes = (k1 + kCoopW - 1) / kCoopW;
+    const double thr_lo = Ar<double>::mul(g.thr, Ar<double>::band_lo()), thr_hi = Ar<double>::mul(g.thr, Ar<double>::band_hi());
+    const int nstripes = (k1 + kCW - 1) / kCW;
     for (int s = 0; s < nstripes && !fin; ++s) {
-      const int c0 = s * kCoopW;
-      const int c1 = min(c0 + kCoopW, k1);
-      if (rank > 0) {
-        const int prev_rows = nk;
-        const int tp = 2 * kCoopTri + kCoopSW * ((prev_rows + 31) / 32);
-        for (int u = (rank - 1) * 32 + warp; u < tp; u += (kClusterSize - 1) * 32) {
-          int cb, rb = 0, half = 0, rc = 0;
-          const bool tri = u < 2 * kCoopTri;
+      const int c0 = s * kCW;
+      const int c1 = min(c0 + kCW, k1);
+      {
+        // one warp per task: 32 rows x 16 columns
+        const int tp = kCTriTasks + 16 * ((nk + 31) / 32);
+        for (int u = rank * 32 + warp; u < tp; u += kClusterSize * 32) {
+          int cb, qd, rb = 0, half = 0, rc = 0;
+          const bool tri = u < kCTriTasks;
           if (tri) {
-            int t = u >> 1;
-            half = u & 1;
-            while (t >= kCoopSW - rb) {
-              t -= kCoopSW - rb;
+            int t = u >> 3;
+            half = (u >> 2) & 1;
+            qd = u & 3;
+            while (t >= kCSW - rb) {
+              t -= kCSW - rb;
               ++rb;
             }
             cb = rb + t;
           } else {
-            const int v = u - 2 * kCoopTri;
-            cb = v % kCoopSW;
-            rc = v / kCoopSW;
+            const int v = u - kCTriTasks;
+            qd = v & 3;
+            cb = (v >> 2) & 3;
+            rc = v >> 4;
           }
-          const int col0 = c0 + cb * 64;
+          const int col0 = c0 + cb * 64 + qd * 16;
           if (col0 >= c1) continue;
-          const int ncols = min(64, c1 - col0);
+          const int ncols = min(16, c1 - col0);
           __syncwarp();
-          for (int j = lane; j < ncols; j += 32) {
-            t_box[j] = ldcg_box(box + col0 + j);
-            t_area[j] = __ldcg(area + col0 + j);
+          if (lane < ncols) {
+            t_box[lane] = ldcg_box(box + col0 + lane);
+            t_area[lane] = __ldcg(area + col0 + lane);
           }
           __syncwarp();
           if (tri) {
-            const int rl = rb * 64 + half * 32 + lane;
+            const int rt = half * 32 + lane;           // row inside the 64x64 tile
+            const int rl = rb * 64 + rt;               // row inside the stripe
             const int row = c0 + rl;
             if (row < c1) {
-              const u64 w = tile_word<double>(ldcg_box(box + row), __ldcg(area + row), t_box, t_area,
-                                              rb == cb ? (half * 32 + lane + 1) : 0, ncols, g.thr);
-              L_sM[rl * kCoopPitch + cb] = w;
+              int jb = 0;
+              if (rb == cb) jb = min(16, max(0, rt - qd * 16 + 1));   // strictly above the diagonal
+              const u32 bits = tile_bits16(ldcg_box(box + row), __ldcg(area + row), t_box, t_area, jb, ncols, g.thr, thr_lo, thr_hi);
+              reinterpret_cast<unsigned short*>(L_sM + rl * kCPitch + cb)[qd] = (unsigned short)bits;
             }
           } else {
-            u64 w = 0;
+            u32 bits = 0;
             const int kidx = rc * 32 + lane;
             if (kidx < nk) {
               const int slot = __ldcg(kept_slot + kidx);
-              w = tile_word<double>(ldcg_box(box + slot), __ldcg(area + slot), t_box, t_area, 0, ncols, g.thr);
+              bits = tile_bits16(ldcg_box(box + slot), __ldcg(area + slot), t_box, t_area, 0, ncols, g.thr, thr_lo, thr_hi);
             }
-            const u32 lo = __reduce_or_sync(0xffffffffu, (u32)w);
-            const u32 hi = __reduce_or_sync(0xffffffffu, (u32)(w >> 32));
-            if (lane == 0) remote_or64(L_removed + cb, ((u64)hi << 32) | lo);
+            bits = __reduce_or_sync(0xffffffffu, bits);
+            if (lane == 0 && bits) atomicOr(reinterpret_cast<u32*>(L_removed + cb) + (qd >> 1), bits << (16 * (qd & 1)));
           }
         }
       }
       cluster.sync();
       if (rank == 0) {
         int f = 0;
-        nk = scan_rows_smem(sM, s_removed, c1 - c0, c0, nk, g.max_keep, kept_slot, &s_keptbits, &s_finish, &f);
-        if (tid < kCoopSW) s_removed[tid] = 0ull;
+        nk = scan_rows_smem(sM, kCPitch, s_removed, c1 - c0, c0, nk, g.max_keep, kept_slot, &s_keptbits, &s_finish, &f);
+        if (tid < kCSW) s_removed[tid] = 0ull;
         if (tid == 0) {
           s_status[0] = nk;
           s_status[1] = f;
@@ -452,7 +485,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       cb->n = k;
       cb->nkept = nk;
       cb->done = finished ? 1 : 0;
-      cb->pad[0] = bail ? 0 : stripes_done;   // first stripe the general path still has to walk
+      cb->pad[0] = bail ? 0 : (stripes_done * kCW) / kCoopW;   // first 1024-box stripe the general path still has to walk
     }
     __syncthreads();
     if (finished) coop_write_outputs<double>(g.a, g.o, cb, b, nk, k);
@@ -461,9 +494,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
 }
 
 static inline size_t cluster_smem_bytes() {
-  const size_t leader = (size_t)kCoopW * kCoopPitch * 8 + kCoopSW * 8 + 64;
-  const size_t tiles = 32 * 64 * (sizeof(double4) + sizeof(double));
-  return leader > tiles ? leader : tiles;
+  return (size_t)kSortMax * 8 + (size_t)kCW * kCPitch * 8 + 8 * 8 + 64 + 32 * 16 * (sizeof(double4) + sizeof(double)) + 64;
 }
 
 }  // namespace mxr
