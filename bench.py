@@ -305,15 +305,51 @@ def run_gpu_arm(args, rank, world, local_rank):
         if st != 0:
             _lib.check(st)
 
+    # pipelined form of the same entry point: two slots, so the H2D copy of batch i+1 overlaps the kernels
+    # of batch i; every step still copies its own inputs in and its own results out inside the timed region
+    outs = [(np.empty((B * post, 5), np.float32), np.empty((B * post,), np.float32), np.empty((B, post), np.int32),
+             np.zeros((B, 2), np.int32)) for _ in range(2)]
+
+    def submit(i):
+        j = i % pool
+        st = lib.mxr_proposal_submit_host(h.ptr, i % 2, ctypes.byref(p), _lib.hptr(cls_np[j]), _lib.hptr(box_np[j]),
+                                          _lib.hptr(info_np[j]), anc, post)
+        if st != 0:
+            _lib.check(st)
+
+    def wait(i):
+        o = outs[i % 2]
+        st = lib.mxr_proposal_wait_host(h.ptr, i % 2, _lib.hptr(o[0]), _lib.hptr(o[1]), _lib.hptr(o[2]), None,
+                                        _lib.hptr(o[3]))
+        if st != 0:
+            _lib.check(st)
+        assert o[3][0, 0] == post
+
+    def run_pipelined(first, count):
+        submit(first)
+        for i in range(first + 1, first + count):
+            submit(i)
+            wait(i - 1)
+        wait(first + count - 1)
+
     for i in range(max(args.warmup, 3)):
         step_host(i)
+    run_pipelined(0, max(args.warmup, 4))
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         step_host(args.warmup + i)
     torch.cuda.synchronize(dev)
+    e2e_sync_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    t0 = time.perf_counter()
+    run_pipelined(args.warmup, args.steps)
+    torch.cuda.synchronize(dev)
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
+    # both forms processed the same last batch: identical keep lists
+    assert np.array_equal(outs[(args.warmup + args.steps - 1) % 2][2], o_keep)
+    e2e_sync_value = world * B * args.steps / e2e_sync_s
     clocks = sampler.stop() if rank == 0 else None
     e2e_value = world * B * args.steps / e2e_s
     N = A * cfg["H"] * cfg["W"]
@@ -327,6 +363,8 @@ def run_gpu_arm(args, rank, world, local_rank):
         step(i)
     prof = h.profile_read()
     h.profile_enable(False)
+    phases = h.proposal_phase_times()
+    phase_mean = {k_: float(np.mean([p_[k_] for p_ in phases])) for k_ in phases[0]} if phases else None
 
     # ---- parity spot check of the last batch against the oracle (not timed) ----
     ok = None
@@ -383,12 +421,16 @@ def run_gpu_arm(args, rank, world, local_rank):
                                                         % (pool, pool * per_batch / 1e6)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": 1e3 * e2e_s / args.steps, "api": "mxr_proposal_forward_host (pinned host buffers)"},
+                    "ms_per_step": 1e3 * e2e_s / args.steps,
+                    "api": "mxr_proposal_submit_host / mxr_proposal_wait_host, two slots (pinned host buffers)",
+                    "one_call_at_a_time": {"value": e2e_sync_value, "ms_per_step": 1e3 * e2e_sync_s / args.steps,
+                                           "api": "mxr_proposal_forward_host"}},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roof,
             "op_hbm": {"achieved": op_gbs, "peak": peak, "unit": "GB/s", "frac": op_gbs / peak,
                        "algorithmic_bytes_per_step": alg["op"]},
             "kernels": per_kernel,
+            "fused_kernel_phases_us": phase_mean,
             "cpu_baseline": {"value": cpu_v, "unit": "images/s", "cores": cores, "kind": "port",
                              "sample": "%d images of the same workload, oracle/restate.py (numpy restatement), one "
                                        "process per core" % n_cpu},

@@ -69,6 +69,10 @@ int mxr_profile_read(mxr_handle_t h, int max_stages, double* total_ms, int32_t* 
 const char* mxr_profile_stage_name(int stage);
 /* Kernels launched by the most recent call on this handle. */
 int mxr_last_launch_count(mxr_handle_t h);
+/* Phase durations (microseconds, %globaltimer stamps taken by the leader CTA) of the most recent fused
+ * proposal launch: us_out[image*9 + i], i = 0 start-up barrier, 1 decode, 2 select, 3 compact, 4 sort,
+ * 5 re-decode, 6 NMS stripes, 7 outputs; [8] = number of 256-box stripes walked.  Synchronises. */
+int mxr_proposal_phase_times(mxr_handle_t h, int max_images, double* us_out, int32_t* images_out);
 
 /* ---- A0  helper/processing/generate_anchor.py:8-72 ---------------------------------- */
 /* Host-side constant table (<= 64 rows); out_anchors: host, (n_ratios*n_scales, 4) f64,
@@ -117,6 +121,19 @@ int mxr_proposal_forward_host(mxr_handle_t h, const mxr_proposal_params* p, cons
                               const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
                               float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
                               int32_t* out_nkeep);
+
+/* Pipelined form of the host entry point (mxr_proposal_forward_host == submit + wait on slot 0).
+ * submit enqueues, on the private stream of `slot` (0 or 1), the H2D copies of the inputs (pinned host
+ * memory recommended), the kernels and the D2H copy of the results into the slot's pinned block, and
+ * returns at once; wait blocks until that slot is finished and copies the results into the caller's
+ * arrays.  Alternating the two slots overlaps the input copy of batch i+1 with the kernels of batch i,
+ * which is how the reference's MXNet engine would feed the op (asnumpy/assign around the callback,
+ * rcnn/rpn/proposal.py:57-63,147-149).  The input arrays must stay valid until wait returns.  Call
+ * mxr_reserve_proposal first: the workspace cannot grow while the other slot is in flight. */
+int mxr_proposal_submit_host(mxr_handle_t h, int slot, const mxr_proposal_params* p, const float* cls_prob,
+                             const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity);
+int mxr_proposal_wait_host(mxr_handle_t h, int slot, float* out_rois, float* out_scores, int32_t* out_keep,
+                           int32_t* out_anchor_index, int32_t* out_nkeep);
 
 /* proposal.py:135-139: rows [nkeep, nkeep+n_pad) of image `image` := row pad_rows[t] (< nkeep).
  * pad_rows: HOST, drawn by the caller as randint(0, nkeep, n_pad). */

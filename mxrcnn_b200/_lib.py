@@ -59,6 +59,7 @@ SIGNATURES = {
     "mxr_profile_read": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p, c_int_p]),
     "mxr_profile_stage_name": (ctypes.c_char_p, [ctypes.c_int]),
     "mxr_last_launch_count": (ctypes.c_int, [_VP]),
+    "mxr_proposal_phase_times": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p, c_int_p]),
     "mxr_generate_anchors": (ctypes.c_int, [ctypes.c_double, c_double_p, ctypes.c_int, c_double_p, ctypes.c_int,
                                             c_double_p]),
     "mxr_reserve_proposal": (ctypes.c_int, [_VP, ctypes.POINTER(ProposalParams)]),
@@ -66,6 +67,9 @@ SIGNATURES = {
                                             ctypes.c_int, _VP, _VP, _VP, _VP, _VP]),
     "mxr_proposal_forward_host": (ctypes.c_int, [_VP, ctypes.POINTER(ProposalParams), _VP, _VP, _VP, c_double_p,
                                                  ctypes.c_int, _VP, _VP, _VP, _VP, _VP]),
+    "mxr_proposal_submit_host": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ProposalParams), _VP, _VP, _VP,
+                                                c_double_p, ctypes.c_int]),
+    "mxr_proposal_wait_host": (ctypes.c_int, [_VP, ctypes.c_int, _VP, _VP, _VP, _VP, _VP]),
     "mxr_proposal_pad": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_int_p, ctypes.c_int,
                                         _VP, _VP]),
     "mxr_nms": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
@@ -158,6 +162,21 @@ class Handle(object):
         check(load().mxr_profile_read(self._h, n, ms, cnt))
         lib = load()
         return {lib.mxr_profile_stage_name(i).decode(): (ms[i], cnt[i]) for i in range(n) if cnt[i]}
+
+    PHASES = ("startup_barrier", "decode_filter", "radix_select", "compact", "head_sort", "redecode", "nms_stripes",
+              "outputs")
+
+    def proposal_phase_times(self, max_images=64):
+        """Per-image phase durations (us) of the last fused proposal launch: list of dicts."""
+        us = (ctypes.c_double * (max_images * 9))()
+        n = ctypes.c_int32(0)
+        check(load().mxr_proposal_phase_times(self._h, max_images, us, ctypes.byref(n)))
+        out = []
+        for b in range(n.value):
+            d = {name: us[b * 9 + i] for i, name in enumerate(self.PHASES)}
+            d["stripes_walked"] = int(us[b * 9 + 8])
+            out.append(d)
+        return out
 
     def last_launch_count(self):
         return int(load().mxr_last_launch_count(self._h))

@@ -84,6 +84,8 @@ int mxr_destroy(mxr_handle_t hh) {
   if (h->d_ws) cudaFree(h->d_ws);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->at_state) free(h->at_state);
+  if (h->prop_state) free(h->prop_state);
+  if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->ev) cudaEventDestroy(h->ev);
   if (h->prof) {
     for (int i = 0; i < h->prof_cap; ++i) {
@@ -147,6 +149,31 @@ const char* mxr_profile_stage_name(int stage) {
 }
 
 int mxr_last_launch_count(mxr_handle_t hh) { return hh ? reinterpret_cast<Handle*>(hh)->last_launches : 0; }
+
+int mxr_proposal_phase_times(mxr_handle_t hh, int max_images, double* us_out, int32_t* images_out) {
+  MXR_REQUIRE(hh != nullptr && us_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
+              "mxr_proposal_phase_times: bad argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  *images_out = 0;
+  if (!h->dbg_ptr || h->dbg_images <= 0) return MXR_OK;
+  MXR_CUDA(cudaDeviceSynchronize());
+  const int n = h->dbg_images < max_images ? h->dbg_images : max_images;
+  unsigned long long* tmp = new unsigned long long[(size_t)n * 16];
+  cudaError_t e = cudaMemcpy(tmp, h->dbg_ptr, (size_t)n * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) {
+    delete[] tmp;
+    set_error("mxr_proposal_phase_times: %s", cudaGetErrorString(e));
+    return MXR_ERR_CUDA;
+  }
+  for (int b = 0; b < n; ++b) {
+    for (int i = 0; i < 8; ++i) us_out[b * 9 + i] = (double)(tmp[b * 16 + i + 1] - tmp[b * 16 + i]) * 1e-3;
+    us_out[b * 9 + 8] = (double)tmp[b * 16 + 9];
+  }
+  delete[] tmp;
+  *images_out = n;
+  return MXR_OK;
+}
 
 int mxr_synchronize(mxr_handle_t hh, void* stream) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_synchronize: NULL handle");

@@ -93,6 +93,10 @@ struct Handle {
   int coop_grid[4];   // co-resident grid size of the cooperative kernels (0: not queried yet)
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
+  unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
+  int dbg_images;
+  cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path
+  void* prop_state;      // per-slot state of mxr_proposal_submit_host / _wait_host (malloc'd, proposal.cu)
 };
 
 // Bracket one kernel launch.  No-ops unless mxr_profile_enable(h, 1) was called.

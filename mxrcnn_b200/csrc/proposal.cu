@@ -1,4 +1,5 @@
 // rcnn/rpn/proposal.py:39-149 -- host side of the proposal operator.
+#include <stdlib.h>
 #include <string.h>
 
 #include "nms_coop.cuh"
@@ -29,6 +30,7 @@ struct Layout {
   int* kept_slot;
   u64* M;
   u64* g_sort_keys;
+  u64* dbg;  // [B][16] phase time stamps of the fused kernel
   // staging for the *_host entry point
   float* d_cls;
   float* d_box;
@@ -83,6 +85,7 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   const size_t m_words = (size_t)L->plan.max_width * (L->plan.max_width / 64);
   L->M = c.take<u64>((size_t)L->B * m_words);
   L->g_sort_keys = L->use_smem_sort ? nullptr : c.take<u64>((size_t)L->B * L->n_pow2_max);
+  L->dbg = c.take<u64>((size_t)L->B * 16);
   if (host_io) {
     const size_t hw = (size_t)L->H * L->W;
     L->d_cls = c.take<float>((size_t)L->B * L->A * hw);  // foreground half only
@@ -221,6 +224,9 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     cl.a = ca.a;
     cl.o = ca.o;
     cl.ctrl = L.ctrl;
+    cl.dbg = L.dbg;
+    h->dbg_ptr = L.dbg;
+    h->dbg_images = L.B;
     const size_t smem_c = cluster_smem_bytes();
     void (*kern)(ClusterArgs) = cluster_items <= 4 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
     const int slot = cluster_items <= 4 ? 4 : 5;
@@ -293,8 +299,8 @@ int mxr_reserve_proposal(mxr_handle_t hh, const mxr_proposal_params* p) {
   Layout L;
   MXR_TRY(make_layout(p, p->post_nms_top_n > 0 ? p->post_nms_top_n : p->num_anchors * p->height * p->width, true,
                       nullptr, &L));
-  MXR_TRY(ensure_device_ws(h, L.total));
-  MXR_TRY(ensure_pinned_ws(h, L.out_bytes));
+  MXR_TRY(ensure_device_ws(h, 2 * L.total));
+  MXR_TRY(ensure_pinned_ws(h, 2 * align_up(L.out_bytes, 256)));
   return MXR_OK;
 }
 
@@ -317,21 +323,40 @@ int mxr_proposal_forward(mxr_handle_t hh, void* stream, const mxr_proposal_param
                  out_keep, out_anchor_index, out_nkeep);
 }
 
-int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, const float* cls_prob,
-                              const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
-                              float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
-                              int32_t* out_nkeep) {
-  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_forward_host: NULL handle");
-  MXR_REQUIRE(cls_prob && bbox_pred && im_info && anchors && out_rois && out_nkeep, MXR_ERR_INVALID,
-              "mxr_proposal_forward_host: NULL array argument");
+// Pipelined host path: two slots, each with its own device staging, stream and pinned result block,
+// so that the H2D copy of one batch overlaps the kernels of the previous one.
+struct HostSlots {
+  Layout L[2];
+  int busy[2];
+};
+
+int mxr_proposal_submit_host(mxr_handle_t hh, int slot, const mxr_proposal_params* p, const float* cls_prob,
+                             const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_submit_host: NULL handle");
+  MXR_REQUIRE(slot == 0 || slot == 1, MXR_ERR_INVALID, "mxr_proposal_submit_host: slot must be 0 or 1");
+  MXR_REQUIRE(cls_prob && bbox_pred && im_info && anchors, MXR_ERR_INVALID, "mxr_proposal_submit_host: NULL array argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
   MXR_CUDA(cudaSetDevice(h->device));
-  Layout L;
+  if (!h->prop_state) {
+    h->prop_state = calloc(1, sizeof(HostSlots));
+    MXR_REQUIRE(h->prop_state != nullptr, MXR_ERR_NOMEM, "mxr_proposal_submit_host: out of host memory");
+  }
+  HostSlots* hs = reinterpret_cast<HostSlots*>(h->prop_state);
+  MXR_REQUIRE(!hs->busy[slot], MXR_ERR_INVALID, "mxr_proposal_submit_host: slot %d still holds results (call wait)", slot);
+  if (!h->stream2) MXR_CUDA(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+  Layout& L = hs->L[slot];
   MXR_TRY(make_layout(p, out_capacity, true, nullptr, &L));
-  MXR_TRY(ensure_device_ws(h, L.total));
-  MXR_TRY(ensure_pinned_ws(h, L.out_bytes));
-  MXR_TRY(make_layout(p, out_capacity, true, h->d_ws, &L));
-  cudaStream_t s = h->stream;
+  const size_t total = L.total, out_bytes = align_up(L.out_bytes, 256);
+  if (2 * total > h->d_bytes || 2 * out_bytes > h->h_bytes) {
+    // growing the blocks would pull the rug from under the other slot
+    MXR_REQUIRE(!hs->busy[1 - slot], MXR_ERR_INVALID,
+                "mxr_proposal_submit_host: workspace must grow while slot %d is in flight; call mxr_reserve_proposal first",
+                1 - slot);
+    MXR_TRY(ensure_device_ws(h, 2 * total));
+    MXR_TRY(ensure_pinned_ws(h, 2 * out_bytes));
+  }
+  MXR_TRY(make_layout(p, out_capacity, true, h->d_ws + (size_t)slot * (h->d_bytes / 2 / 256 * 256), &L));
+  cudaStream_t s = slot ? h->stream2 : h->stream;
   const size_t hw = (size_t)L.H * L.W;
   // only the foreground half of cls_prob crosses the bus (proposal.py:57)
   const size_t fg_bytes = (size_t)L.A * hw * sizeof(float);
@@ -346,14 +371,31 @@ int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, con
   int* d_nkeep = reinterpret_cast<int*>(L.d_out + L.off_nkeep);
   MXR_TRY(enqueue(h, s, p, L, L.d_cls, (size_t)L.A * hw, 0, L.d_box, L.d_info, anchors, d_rois, d_scores, d_keep,
                   d_anchor, d_nkeep));
-  MXR_CUDA(cudaMemcpyAsync(h->h_pin, L.d_out, L.out_bytes, cudaMemcpyDeviceToHost, s));
-  MXR_CUDA(cudaStreamSynchronize(s));
+  MXR_CUDA(cudaMemcpyAsync(h->h_pin + (size_t)slot * (h->h_bytes / 2 / 256 * 256), L.d_out, L.out_bytes,
+                           cudaMemcpyDeviceToHost, s));
+  hs->busy[slot] = 1;
+  return MXR_OK;
+}
+
+int mxr_proposal_wait_host(mxr_handle_t hh, int slot, float* out_rois, float* out_scores, int32_t* out_keep,
+                           int32_t* out_anchor_index, int32_t* out_nkeep) {
+  MXR_REQUIRE(hh != nullptr && out_rois != nullptr && out_nkeep != nullptr, MXR_ERR_INVALID,
+              "mxr_proposal_wait_host: NULL argument");
+  MXR_REQUIRE(slot == 0 || slot == 1, MXR_ERR_INVALID, "mxr_proposal_wait_host: slot must be 0 or 1");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  HostSlots* hs = reinterpret_cast<HostSlots*>(h->prop_state);
+  MXR_REQUIRE(hs && hs->busy[slot], MXR_ERR_INVALID, "mxr_proposal_wait_host: nothing was submitted to slot %d", slot);
+  MXR_CUDA(cudaSetDevice(h->device));
+  const Layout& L = hs->L[slot];
+  MXR_CUDA(cudaStreamSynchronize(slot ? h->stream2 : h->stream));
+  hs->busy[slot] = 0;
+  const char* src = h->h_pin + (size_t)slot * (h->h_bytes / 2 / 256 * 256);
   const size_t rows = (size_t)L.B * L.out_rows;
-  memcpy(out_rois, h->h_pin, rows * 5 * sizeof(float));
-  if (out_scores) memcpy(out_scores, h->h_pin + L.off_scores, rows * sizeof(float));
-  if (out_keep) memcpy(out_keep, h->h_pin + L.off_keep, rows * sizeof(int));
-  if (out_anchor_index) memcpy(out_anchor_index, h->h_pin + L.off_anchor, rows * sizeof(int));
-  memcpy(out_nkeep, h->h_pin + L.off_nkeep, (size_t)L.B * 2 * sizeof(int));
+  memcpy(out_rois, src, rows * 5 * sizeof(float));
+  if (out_scores) memcpy(out_scores, src + L.off_scores, rows * sizeof(float));
+  if (out_keep) memcpy(out_keep, src + L.off_keep, rows * sizeof(int));
+  if (out_anchor_index) memcpy(out_anchor_index, src + L.off_anchor, rows * sizeof(int));
+  memcpy(out_nkeep, src + L.off_nkeep, (size_t)L.B * 2 * sizeof(int));
   for (int b = 0; b < L.B; ++b) {
     if (out_nkeep[b * 2 + 1] & 1) {
       set_error("there is nan in input scores or bbox_deltas (image %d)", b);
@@ -361,6 +403,15 @@ int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, con
     }
   }
   return MXR_OK;
+}
+
+int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, const float* cls_prob,
+                              const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity,
+                              float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor_index,
+                              int32_t* out_nkeep) {
+  MXR_REQUIRE(out_rois && out_nkeep, MXR_ERR_INVALID, "mxr_proposal_forward_host: NULL array argument");
+  MXR_TRY(mxr_proposal_submit_host(hh, 0, p, cls_prob, bbox_pred, im_info, anchors, out_capacity));
+  return mxr_proposal_wait_host(hh, 0, out_rois, out_scores, out_keep, out_anchor_index, out_nkeep);
 }
 
 int mxr_proposal_pad(mxr_handle_t hh, void* stream, int image, int rows_per_image, int nkeep, const int32_t* pad_rows,

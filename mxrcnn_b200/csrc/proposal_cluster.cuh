@@ -43,7 +43,18 @@ struct ClusterArgs {
   NmsArrays<double> a;
   NmsOutputs o;
   Ctrl* ctrl;
+  u64* dbg;          // optional [b][16] globaltimer stamps at the phase boundaries (leader CTA), or null
 };
+
+__device__ __forceinline__ u64 global_ns() {
+  u64 t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define MXR_STAMP(i)                                                              \
+  do {                                                                            \
+    if (g.dbg && rank == 0 && tid == 0) g.dbg[(size_t)b * 16 + (i)] = global_ns(); \
+  } while (0)
 
 __device__ __forceinline__ double4 ldcg_box(const double4* p) {
   const double2 a = __ldcg(reinterpret_cast<const double2*>(p));
@@ -56,6 +67,34 @@ __device__ __forceinline__ void remote_or64(u64* p, u64 v) {
   const u32 lo = (u32)v, hi = (u32)(v >> 32);
   if (lo) atomicOr(q, lo);
   if (hi) atomicOr(q + 1, hi);
+}
+
+// Descending bitonic sort of n_pow2 <= 1024 distinct 64-bit keys, one key per thread (blockDim.x == 1024):
+// strides below 32 are warp shuffles, only strides >= 32 go through shared memory (15 of the 55 stages).
+__device__ __forceinline__ void bitonic_sort_1024_regs(u64* buf, int n_pow2) {
+  const int t = threadIdx.x;
+  u64 v = buf[t];  // entries beyond the real keys are zero-padded by the caller up to n_pow2; beyond that unused
+  for (int size = 2; size <= n_pow2; size <<= 1) {
+    const bool desc = (t & size) == 0;
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      u64 other;
+      if (stride < 32) {
+        other = __shfl_xor_sync(0xffffffffu, v, stride);
+      } else {
+        __syncthreads();
+        buf[t] = v;
+        __syncthreads();
+        other = buf[t ^ stride];
+      }
+      const bool lower = (t & stride) == 0;
+      const bool take_max = (lower == desc);
+      const bool other_gt = other > v;
+      v = (take_max == other_gt) ? other : v;
+    }
+  }
+  __syncthreads();
+  buf[t] = v;
+  __syncthreads();
 }
 
 // 16 columns of one row: bit j set when column j is suppressed by the row box (nms.py:25-36).
@@ -193,7 +232,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     if (tid < 2) s_status[tid] = 0;
   }
   if (tid < 4) s_local[tid] = 0;
+  MXR_STAMP(0);
   cluster.sync();
+  MXR_STAMP(1);
 
   // ---- P1: decode + clip + min-size filter (proposal.py:77-120); keys stay in registers ----
   const int hwc = dg.hc * dg.wc;
@@ -264,6 +305,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   const int nan_flag = s_local[3] ? 1 : 0;
   const int k = (g.pre_nms > 0) ? min(g.pre_nms, n_valid) : n_valid;  // proposal.py:124-125
   const int k1 = min(g.head, k);
+  MXR_STAMP(2);
 
   // ---- P2: radix select of the head threshold on the 32-bit score keys ----
   bool bail = false;   // a run of equal scores is cut by the head boundary: leave it to the general path
@@ -328,6 +370,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     T = prefix;
   }
 
+  MXR_STAMP(3);
   int nk = 0, fin = 0, stripes_done = 0;
   if (!bail && k1 > 0) {
     // ---- P3: selected composites go straight into the leader's sort buffer ----
@@ -367,9 +410,19 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     if (rank == 0)
       for (int i = k1 + tid; i < n_pow2; i += blockDim.x) sortbuf[i] = 0ull;
     cluster.sync();
+    MXR_STAMP(4);
     // ---- P4: the leader orders the head: (score desc, row index asc) -- see topk_body ----
-    if (rank == 0) bitonic_sort_desc_u64(sortbuf, n_pow2);
+    if (rank == 0) {
+      if (n_pow2 <= 1024) {
+        for (int i = n_pow2 + tid; i < 1024; i += blockDim.x) sortbuf[i] = 0ull;
+        __syncthreads();
+        bitonic_sort_1024_regs(sortbuf, n_pow2);
+      } else {
+        bitonic_sort_desc_u64(sortbuf, n_pow2);
+      }
+    }
     cluster.sync();
+    MXR_STAMP(5);
     // ---- P5: all CTAs re-decode their slice of the head into processing order ----
     {
       const int per = (k1 + kClusterSize - 1) / kClusterSize;
@@ -390,6 +443,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     }
     __threadfence();
     cluster.sync();
+    MXR_STAMP(6);
     // ---- P6: stripes of 256 boxes (cluster barriers cost ~0.2 us, so narrow stripes keep the
     //      evaluated IoU pairs close to what the greedy walk really needs) ----
     const double4* box = g.a.box + (size_t)b * g.a.cap;
@@ -475,6 +529,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       __syncthreads();
     }
   }
+  MXR_STAMP(7);
   // ---- P7: results, or hand-over state for the general path ----
   if (rank == 0) {
     const bool finished = !bail && (fin || k1 >= k);
@@ -491,10 +546,12 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     if (finished) coop_write_outputs<double>(g.a, g.o, cb, b, nk, k);
   }
   cluster.sync();  // nobody leaves while its shared memory may still be addressed
+  MXR_STAMP(8);
+  if (g.dbg && rank == 0 && tid == 0) g.dbg[(size_t)b * 16 + 9] = (u64)stripes_done;
 }
 
 static inline size_t cluster_smem_bytes() {
-  return (size_t)kSortMax * 8 + (size_t)kCW * kCPitch * 8 + 8 * 8 + 64 + 32 * 16 * (sizeof(double4) + sizeof(double)) + 64;
+  return (size_t)kSortMax * 8 + (size_t)kCW * kCPitch * 8 + 8 * 8 + 32 * 16 * (sizeof(double4) + sizeof(double)) + 256;
 }
 
 }  // namespace mxr
