@@ -74,6 +74,10 @@ int mxr_last_launch_count(mxr_handle_t h);
  * 5 re-decode, 6 NMS stripes, 7 outputs; [8] = number of 256-box stripes walked.  Synchronises. */
 int mxr_proposal_phase_times(mxr_handle_t h, int max_images, double* us_out, int32_t* images_out);
 
+/* Measured non-tensor ALU throughput of this GPU (Gop/s; streams of independent multiplies and adds,
+ * no FMA contraction) -- the denominator of the NMS kernels' ALU roofline in bench.py. */
+int mxr_bench_alu_peak(mxr_handle_t h, int dtype, double* gops_out);
+
 /* ---- A0  helper/processing/generate_anchor.py:8-72 ---------------------------------- */
 /* Host-side constant table (<= 64 rows); out_anchors: host, (n_ratios*n_scales, 4) f64,
  * ratio-major / scale-minor row order. */

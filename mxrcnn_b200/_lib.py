@@ -59,6 +59,7 @@ SIGNATURES = {
     "mxr_profile_read": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p, c_int_p]),
     "mxr_profile_stage_name": (ctypes.c_char_p, [ctypes.c_int]),
     "mxr_last_launch_count": (ctypes.c_int, [_VP]),
+    "mxr_bench_alu_peak": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p]),
     "mxr_proposal_phase_times": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p, c_int_p]),
     "mxr_generate_anchors": (ctypes.c_int, [ctypes.c_double, c_double_p, ctypes.c_int, c_double_p, ctypes.c_int,
                                             c_double_p]),

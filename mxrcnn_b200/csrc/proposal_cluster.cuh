@@ -131,25 +131,24 @@ __device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_r
       const u64 word0 = s_removed[blk];
       const int nvalid = min(64, rows - blk * 64);
       const u64 valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1ull);
-      const u64 d0 = (blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * pitch + blk] : 0ull;
-      const u64 d1 = (blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * pitch + blk] : 0ull;
-      u32 lo = (u32)(word0 | ~valid), hi = (u32)((word0 | ~valid) >> 32);
-      const u32 d0lo = (u32)d0, d0hi = (u32)(d0 >> 32), d1hi = (u32)(d1 >> 32);
-#pragma unroll
-      for (int t = 0; t < 32; ++t) {
-        const u32 rlo = __shfl_sync(0xffffffffu, d0lo, t);
-        const u32 rhi = __shfl_sync(0xffffffffu, d0hi, t);
-        if (!((lo >> t) & 1u)) {
-          lo |= rlo;
-          hi |= rhi;
-        }
+      const u64 alive = ~word0 & valid;
+      // Diagonal tile, stored as its LOWER triangle: bit j of row i (j < i) says "j suppresses i" (the IoU
+      // predicate is symmetric bit for bit).  Greedy keep is the unique fixed point of
+      //   keep_i = alive_i and no kept j < i suppresses i ;
+      // iterating from keep = alive fixes at least one more leading position per round, and in practice
+      // converges in a handful of rounds instead of a 64-step dependent chain.
+      const u64 m0 = ((blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * pitch + blk] : 0ull) & ((1ull << tid) - 1ull);
+      const u64 m1 = ((blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * pitch + blk] : 0ull) & ((1ull << (tid + 32)) - 1ull);
+      const bool a0 = (alive >> tid) & 1ull, a1 = (alive >> (tid + 32)) & 1ull;
+      u64 keep = alive;
+      for (int it = 0; it < 64; ++it) {
+        const u32 k0 = __ballot_sync(0xffffffffu, a0 && (m0 & keep) == 0ull);
+        const u32 k1 = __ballot_sync(0xffffffffu, a1 && (m1 & keep) == 0ull);
+        const u64 nxt = ((u64)k1 << 32) | k0;
+        if (nxt == keep) break;
+        keep = nxt;
       }
-#pragma unroll
-      for (int t = 0; t < 32; ++t) {
-        const u32 rhi = __shfl_sync(0xffffffffu, d1hi, t);
-        if (!((hi >> t) & 1u)) hi |= rhi;
-      }
-      u64 kept = ~(((u64)hi << 32) | lo) & valid;
+      u64 kept = keep;
       int fin = 0;
       if (max_keep > 0 && nk + __popcll(kept) >= max_keep) {
         int want = max_keep - nk;
@@ -457,7 +456,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       {
         // one warp per task: 32 rows x 16 columns
         const int tp = kCTriTasks + 16 * ((nk + 31) / 32);
-        for (int u = rank * 32 + warp; u < tp; u += kClusterSize * 32) {
+        // task u runs on CTA u % 8, warp u / 8: a stripe's few dozen tasks spread over all 8 SMs' FP64 pipes
+        for (int u = warp * kClusterSize + rank; u < tp; u += kClusterSize * 32) {
           int cb, qd, rb = 0, half = 0, rc = 0;
           const bool tri = u < kCTriTasks;
           if (tri) {
@@ -489,9 +489,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
             const int rl = rb * 64 + rt;               // row inside the stripe
             const int row = c0 + rl;
             if (row < c1) {
-              int jb = 0;
-              if (rb == cb) jb = min(16, max(0, rt - qd * 16 + 1));   // strictly above the diagonal
-              const u32 bits = tile_bits16(ldcg_box(box + row), __ldcg(area + row), t_box, t_area, jb, ncols, g.thr, thr_lo, thr_hi);
+              int je = ncols;
+              if (rb == cb) je = min(ncols, max(0, rt - qd * 16));   // diagonal tile: strictly BELOW the diagonal
+              const u32 bits = tile_bits16(ldcg_box(box + row), __ldcg(area + row), t_box, t_area, 0, je, g.thr, thr_lo, thr_hi);
               reinterpret_cast<unsigned short*>(L_sM + rl * kCPitch + cb)[qd] = (unsigned short)bits;
             }
           } else {
@@ -506,7 +506,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
           }
         }
       }
+      if (s == 0) MXR_STAMP(10);
       cluster.sync();
+      if (s == 0) MXR_STAMP(11);
       if (rank == 0) {
         int f = 0;
         nk = scan_rows_smem(sM, kCPitch, s_removed, c1 - c0, c0, nk, g.max_keep, kept_slot, &s_keptbits, &s_finish, &f);
@@ -517,7 +519,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
         }
         __threadfence();
       }
+      if (s == 0) MXR_STAMP(12);
       cluster.sync();
+      if (s == 0) MXR_STAMP(13);
       if (tid == 0) {
         s_local[2] = L_status[0];
         s_local[3] = L_status[1];
