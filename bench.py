@@ -366,6 +366,51 @@ def run_gpu_arm(args, rank, world, local_rank):
     phases = h.proposal_phase_times()
     phase_mean = {k_: float(np.mean([p_[k_] for p_ in phases])) for k_ in phases[0]} if phases else None
 
+    # ---- measured ALU peaks (in-repo micro-benchmark, no FMA contraction) for the NMS roofline ----
+    alu = {}
+    for nm, code in (("f64", 1), ("f32", 0)):
+        gv = ctypes.c_double(0)
+        _lib.check(lib.mxr_bench_alu_peak(h.ptr, code, ctypes.byref(gv)))
+        alu[nm] = gv.value
+
+    # ---- saturating batch (not the headline): 256 images in one launch = 132 MB of inputs (> L2),
+    #      14 waves of 8-CTA clusters; shows the throughput asymptote of the same kernels ----
+    sat = None
+    if rank == 0:
+        SB = 256
+        reps = (SB + pool * B - 1) // (pool * B)
+        cls_s = cls_d.reshape(pool * B, 2 * A, cfg["H"], cfg["W"]).repeat(reps, 1, 1, 1)[:SB].contiguous()
+        box_s = box_d.reshape(pool * B, 4 * A, cfg["H"], cfg["W"]).repeat(reps, 1, 1, 1)[:SB].contiguous()
+        info_s = info_d.reshape(pool * B, 3).repeat(reps, 1)[:SB].contiguous()
+        ps = _lib.ProposalParams(SB, A, cfg["H"], cfg["W"], 0, 0, float(cfg["feat_stride"]), cfg["pre"], post,
+                                 cfg["thresh"], float(cfg["min_size"]), 0)
+        rois_s = torch.zeros((SB * post, 5), dtype=torch.float32, device=dev)
+        nk_s = torch.zeros((SB, 2), dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)
+
+        def step_sat():
+            st = lib.mxr_proposal_forward(h.ptr, sp, ctypes.byref(ps), cls_s.data_ptr(), box_s.data_ptr(),
+                                          info_s.data_ptr(), anc, post, rois_s.data_ptr(), None, None, None,
+                                          nk_s.data_ptr())
+            if st != 0:
+                _lib.check(st)
+
+        for _ in range(3):
+            step_sat()
+        torch.cuda.synchronize(dev)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        nsat = 20
+        for _ in range(nsat):
+            step_sat()
+        s1.record(stream)
+        torch.cuda.synchronize(dev)
+        sat_ms = s0.elapsed_time(s1) / nsat
+        assert int(nk_s[:, 0].min()) == post
+        sat = {"batch": SB, "value": SB / (sat_ms * 1e-3), "unit": "images/s", "ms_per_step": sat_ms,
+               "op_hbm_gbs": SB * (20 * A * cfg["H"] * cfg["W"] + 12 + 24 * post) / (sat_ms * 1e-3) / 1e9}
+        del cls_s, box_s, info_s, rois_s
+
     # ---- parity spot check of the last batch against the oracle (not timed) ----
     ok = None
     if rank == 0:
@@ -406,6 +451,20 @@ def run_gpu_arm(args, rank, world, local_rank):
             roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                     "us_per_launch": d["us_per_launch"], "share_of_step": d["share"]}
+        # ALU view of the fused kernel's NMS phase (BASELINE.json: "NMS by SM FP32/ALU-pipe utilisation"):
+        # IoU pairs actually evaluated (256-box stripes: in-stripe triangle + kept-so-far x stripe, the latter
+        # bounded by post x 256) x 15 FP ops per pair over the measured NMS-phase time
+        roof_alu = None
+        if phase_mean and phase_mean.get("nms_stripes"):
+            stripes = phase_mean["stripes_walked"]
+            pairs = B * (stripes * (256 * 255 // 2) + max(0.0, stripes - 1) * 0.5 * post * 256)
+            gflops = pairs * 15 / (phase_mean["nms_stripes"] * 1e-6) / 1e9
+            roof_alu = {"phase": "nms_stripes of proposal_cluster_kernel", "bound": "alu-f64", "achieved": gflops,
+                        "peak": alu["f64"], "unit": "Gop/s", "frac": gflops / alu["f64"],
+                        "pairs_evaluated_per_launch": pairs, "ops_per_pair": 15,
+                        "full_triangle_pairs_per_launch": B * 17997000,
+                        "peak_source": "mxr_bench_alu_peak (independent DADD/DMUL streams, -fmad=false)",
+                        "f32_peak_gops": alu["f32"]}
         # whole-op HBM fraction (SURVEY.md 8d mandatory I/O per image)
         op_gbs = alg["op"] / (ms * 1e-3 / args.steps) / 1e9
         cores = host_cores()
@@ -427,6 +486,8 @@ def run_gpu_arm(args, rank, world, local_rank):
                                            "api": "mxr_proposal_forward_host"}},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roof,
+            "roofline_alu": roof_alu,
+            "saturating_batch": sat,
             "op_hbm": {"achieved": op_gbs, "peak": peak, "unit": "GB/s", "frac": op_gbs / peak,
                        "algorithmic_bytes_per_step": alg["op"]},
             "kernels": per_kernel,
