@@ -213,6 +213,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version there)
         import torch.distributed as dist_mod
         dist = dist_mod
         dist.init_process_group("nccl", device_id=dev)

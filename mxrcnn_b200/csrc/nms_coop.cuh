@@ -272,17 +272,6 @@ __global__ void __launch_bounds__(1024, 1) nms_coop_kernel(CoopArgs<T> g, Tier2 
   const int warp = threadIdx.x >> 5;
   const int n64 = (max(g.n_max, 1) + 63) & ~63;
   const int nstripes = (n64 + kCoopW - 1) / kCoopW;
-  if (g.tier2_at == -2) {
-    // tail of the fused cluster kernel: whatever is not done needs the full candidate order first
-    int remaining = 0;
-    for (int b = threadIdx.x; b < g.B; b += blockDim.x) remaining |= ld_ctrl(g.ctrl + b).done ? 0 : 1;
-    if (!__syncthreads_or(remaining)) return;  // the usual case: nothing left, no grid barrier needed
-    for (int b = blockIdx.x; b < g.B; b += gridDim.x) {
-      if (!ld_ctrl(g.ctrl + b).done && t2.wanted(b)) t2.run(b, g.ctrl, coop_smem, s_st, &s_cnt);
-      __syncthreads();
-    }
-    grid.sync();
-  }
   for (int s = 0; s < nstripes; ++s) {
     const int c0 = s * kCoopW;
     // anything left to do?  (ctrl is stable here: written before the previous grid.sync / kernel boundary)

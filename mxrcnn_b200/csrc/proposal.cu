@@ -140,12 +140,16 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   pg.cls_img_stride = cls_img_stride;
   pg.cls_fg_offset = cls_fg_offset;
   h->last_launches = 0;
-  MXR_CUDA(cudaMemsetAsync(L.ctrl, 0, L.zero_bytes, s));
-  // Fast path: the fused cluster kernel (one launch, one 8-CTA cluster per image).  It needs an
-  // image's anchors to fit 8 CTAs x 12 keys x 1024 threads; MXRCNN_B200_NO_CLUSTER=1 forces the
-  // multi-kernel path (used by the tests to cover both).
+  // Fast path: the fused cluster kernel (ONE launch for the whole op, one 8-CTA cluster per image).  It needs
+  // an image's anchors to fit 8 CTAs x 12 keys x 1024 threads and the pre-NMS list to fit the leader's
+  // shared-memory sort buffer; otherwise, or with MXRCNN_B200_NO_CLUSTER=1 (used by the tests to cover both),
+  // the multi-kernel path runs.
   const int cluster_items = (L.n_crop + kClusterSize * 1024 - 1) / (kClusterSize * 1024);
-  const bool use_cluster = cluster_items <= 12 && !h->no_cluster;
+  int sort_cap = pow2_ceil(L.n_max > L.head ? L.n_max : L.head);
+  if (sort_cap < 1024) sort_cap = 1024;
+  const bool use_cluster = cluster_items <= 12 && sort_cap <= kClusterSortMax && !h->no_cluster;
+  // the fused kernel initialises everything it uses; only the multi-kernel path needs zeroed control blocks
+  if (!use_cluster) MXR_CUDA(cudaMemsetAsync(L.ctrl, 0, L.zero_bytes, s));
   if (!use_cluster) {
     const int n_threads = L.n_crop > L.n_full ? L.n_crop : L.n_full;
     dim3 g1((n_threads + 255) / 256, L.B);
@@ -220,14 +224,14 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     cl.head = L.head;
     cl.max_keep = ca.max_keep;
     cl.thr = p->nms_thresh;
-    cl.keys = L.keys;
+    cl.sort_cap = sort_cap;
     cl.a = ca.a;
     cl.o = ca.o;
     cl.ctrl = L.ctrl;
     cl.dbg = L.dbg;
     h->dbg_ptr = L.dbg;
     h->dbg_images = L.B;
-    const size_t smem_c = cluster_smem_bytes();
+    const size_t smem_c = cluster_smem_bytes(sort_cap);
     void (*kern)(ClusterArgs) = cluster_items <= 4 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
     const int slot = cluster_items <= 4 ? 4 : 5;
     if ((int)smem_c > h->smem_attr[slot]) {
@@ -250,7 +254,8 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     prof_begin(h, s, ST_CLUSTER);
     MXR_CUDA(cudaLaunchKernelEx(&cfg, kern, cl));
     prof_end(h, s);
-    ca.tier2_at = -2;  // the general kernel below only picks up what the cluster kernel left undone
+    MXR_CUDA(cudaGetLastError());
+    return MXR_OK;  // the fused kernel settles every image itself
   }
   ProposalTier2 t2;
   t2.tc = tc;
@@ -263,6 +268,8 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   if (h->coop_grid[0] == 0 || (int)smem2 > h->smem_attr[3]) {
     MXR_CUDA(cudaFuncSetAttribute(nms_coop_kernel<double, ProposalTier2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem2));
+    MXR_CUDA(cudaFuncSetAttribute(nms_coop_kernel<double, ProposalTier2>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
     h->smem_attr[3] = (int)smem2;
     int per_sm = 0, sms = 0;
     MXR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_coop_kernel<double, ProposalTier2>, 1024, smem2));

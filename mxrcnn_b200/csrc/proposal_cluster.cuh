@@ -10,9 +10,11 @@
 //   P6 per 1024-box stripe: the other CTAs evaluate the IoU bit tiles and store them directly into
 //      the leader's shared bit matrix (DSMEM), the leader walks the stripe greedily
 //   P7 the leader writes rois / scores / keep lists.
-// Anything the head cannot settle (post-NMS quota not reached within the head, score ties cut by
-// the head boundary) is left, with its state in global memory, to the general cooperative kernel
-// (nms_coop.cuh), which is launched right after and returns at once when nothing is left.
+// Greedy NMS walks the candidate list in order and usually fills its post-NMS quota long before the
+// tail of the list matters, so only the HEAD of the order (<= 4096 boxes) is selected and sorted up
+// front.  If the head does not settle the image (quota not reached, or a run of equal scores is cut
+// by the head boundary) the same cluster selects and sorts the full pre-NMS list and carries on;
+// the kept list and every stripe already walked stay valid because the head is a prefix of it.
 #pragma once
 #include <cooperative_groups.h>
 
@@ -26,7 +28,7 @@ static const int kCW = 256;        // stripe width inside the cluster kernel (cl
 static const int kCSW = 4;         // words per stripe row
 static const int kCPitch = 5;      // shared-memory row pitch in words
 static const int kCTriTasks = 80;  // 10 upper-triangle tiles x 2 row halves x 4 column quarters
-static const int kSortMax = 4096;  // head capacity of the leader's sort buffer
+static const int kClusterSortMax = 16384;  // largest list the leader sorts in shared memory (128 KiB)
 
 struct ClusterArgs {
   ProposalGeom pg;
@@ -39,7 +41,7 @@ struct ClusterArgs {
   int head;          // sorted prefix handled here (multiple of 64, <= 4096)
   int max_keep;      // > 0: post_nms_top_n
   double thr;
-  u32* keys;         // [b][n_crop] global copy of the keys for the deferred full sort
+  int sort_cap;      // u64 slots of the leader's sort buffer (power of two >= the largest list sorted)
   NmsArrays<double> a;
   NmsOutputs o;
   Ctrl* ctrl;
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   namespace cgx = cooperative_groups;
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ u32 s_hist[256];
-  __shared__ u32 s_ghist[4][256];   // leader: cluster-wide digit histograms, one per pass
+  __shared__ u32 s_ghist[12][256];  // leader: cluster-wide digit histograms: head select 0..3, full select 4..10
   __shared__ int s_cnt[4];          // leader: n_valid, nan
   __shared__ int s_sel[kClusterSize];  // leader: selected count of each CTA
   __shared__ int s_status[2];       // leader: kept so far, quota reached
@@ -212,8 +214,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   const ProposalGeom& pg = g.pg;
   const DecodeGeom& dg = pg.g;
   // leader-resident structures, addressed through distributed shared memory
-  u64* sortbuf = reinterpret_cast<u64*>(dyn_smem);                           // leader: [kSortMax] head sort buffer
-  u64* sM = sortbuf + kSortMax;                                              // leader: [256][5] bit rows of one stripe
+  u64* sortbuf = reinterpret_cast<u64*>(dyn_smem);                           // leader: [sort_cap] sort buffer
+  u64* sM = sortbuf + g.sort_cap;                                            // leader: [256][5] bit rows of one stripe
   u64* s_removed = sM + kCW * kCPitch;                                       // leader: [4]
   double4* t_box = reinterpret_cast<double4*>(s_removed + 8) + warp * 16;    // every CTA: per-warp column staging
   double* t_area = reinterpret_cast<double*>(reinterpret_cast<double4*>(s_removed + 8) + 32 * 16) + warp * 16;
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   int* L_sel = cluster.map_shared_rank(s_sel, 0);
   int* L_status = cluster.map_shared_rank(s_status, 0);
   if (rank == 0) {
-    for (int i = tid; i < 4 * 256; i += blockDim.x) (&s_ghist[0][0])[i] = 0;
+    for (int i = tid; i < 12 * 256; i += blockDim.x) (&s_ghist[0][0])[i] = 0;
     if (tid < 4) s_cnt[tid] = 0;
     if (tid < kCSW) s_removed[tid] = 0ull;
     if (tid < 2) s_status[tid] = 0;
@@ -269,7 +271,6 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
         const bool valid = passes_min_size(bx, g.min_size, im_s);
         nan = (s != s) || dnan;
         key = valid ? score_key32(s) : 0u;
-        g.keys[(size_t)b * pg.n_crop + q] = key;
       }
       rk[i] = key;
       nvalid += __popc(__ballot_sync(0xffffffffu, key != 0u));
@@ -306,23 +307,30 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   const int k1 = min(g.head, k);
   MXR_STAMP(2);
 
-  // ---- P2: radix select of the head threshold on the 32-bit score keys ----
-  bool bail = false;   // a run of equal scores is cut by the head boundary: leave it to the general path
-  u32 T = 1u;
-  if (k1 > 0 && k1 < n_valid) {
-    u32 prefix = 0;
-    int k_rem = k1;
+  auto p_of_item = [&](int i) -> u32 { return (u32)q_to_p(q_begin + tid + i * 1024, hwc, dg.A); };
+
+  // ---- radix select over the cluster: threshold T such that exactly k_sel valid composites
+  //      (score key << 32 | row index) are >= T.  The four key bytes come first; the row-index bytes are
+  //      only looked at when a run of equal scores straddles the cut and use_p is set.  Per-CTA digit
+  //      histograms are summed in the leader's shared memory with DSMEM atomics and read back by all.
+  //      Returns false when the cut is not exact (only possible without use_p). ----
+  auto cluster_select = [&](int k_sel, int hist_base, bool use_p, u64* T_out) -> bool {
+    u64 prefix = 0;
+    int k_rem = k_sel;
     u32 cnt = 0;
-    for (int pass = 0; pass < 4; ++pass) {
-      const int shift = 24 - 8 * pass;
+    const int npass = use_p ? 7 : 4;
+    for (int pass = 0; pass < npass; ++pass) {
+      const int shift = pass < 4 ? 56 - 8 * pass : 16 - 8 * (pass - 4);
       if (tid < 256) s_hist[tid] = 0;
       __syncthreads();
 #pragma unroll
       for (int i = 0; i < ITEMS; ++i) {
         const u32 key = rk[i];
         bool valid = key != 0u;
-        if (valid && pass > 0) valid = ((key ^ prefix) >> (shift + 8)) == 0u;
-        const u32 digit = (key >> shift) & 255u;
+        u64 c = (u64)key << 32;
+        if (pass >= 4) c |= p_of_item(i);
+        if (valid && pass > 0) valid = ((c ^ prefix) >> (shift + 8)) == 0ull;
+        const u32 digit = (u32)(c >> shift) & 255u;
         const u32 active = __ballot_sync(0xffffffffu, valid);
         if (valid) {
           const u32 peers = __match_any_sync(active, digit);
@@ -330,9 +338,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
         }
       }
       __syncthreads();
-      if (tid < 256 && s_hist[tid]) atomicAdd(L_ghist + pass * 256 + tid, s_hist[tid]);
+      if (tid < 256 && s_hist[tid]) atomicAdd(L_ghist + (hist_base + pass) * 256 + tid, s_hist[tid]);
       cluster.sync();
-      if (tid < 256) s_hist[tid] = L_ghist[pass * 256 + tid];
+      if (tid < 256) s_hist[tid] = L_ghist[(hist_base + pass) * 256 + tid];
       __syncthreads();
       if (warp == 0) {
         u32 mine = 0;
@@ -359,25 +367,33 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
         }
       }
       __syncthreads();
-      prefix |= s_st[0] << shift;
+      prefix |= (u64)s_st[0] << shift;
       k_rem = (int)s_st[1];
       cnt = s_st[2];
       __syncthreads();
       if ((int)cnt == k_rem) break;
     }
-    bail = ((int)cnt != k_rem);
-    T = prefix;
-  }
+    *T_out = prefix;
+    return (int)cnt == k_rem;
+  };
 
-  MXR_STAMP(3);
-  int nk = 0, fin = 0, stripes_done = 0;
-  if (!bail && k1 > 0) {
-    // ---- P3: selected composites go straight into the leader's sort buffer ----
-    const int n_pow2 = max(2, (int)(1u << (32 - __clz(k1 - 1))));
+  // ---- compact the k_sel selected composites into the leader's sort buffer (DSMEM stores), let the
+  //      leader order them by (score desc, row index ASC) -- nms.py:19 re-sorts the already descending list,
+  //      which reverses runs of equal scores -- and re-decode them, spread over all CTAs, into processing order ----
+  auto sort_and_redecode = [&](int k_sel, u64 T, int stamp) {
+    const int n_pow2 = max(2, (int)(1u << (32 - __clz(k_sel - 1))));
+    const bool need_p = (u32)T != 0u;  // the threshold cuts inside a run of equal scores
+    auto selected = [&](int i) -> bool {
+      const u32 key = rk[i];
+      if (key == 0u) return false;
+      const u64 c = ((u64)key << 32) | ((need_p && key == (u32)(T >> 32)) ? p_of_item(i) : 0xffffffffu);
+      return c >= T;
+    };
     {
       int mine = 0;
 #pragma unroll
-      for (int i = 0; i < ITEMS; ++i) mine += __popc(__ballot_sync(0xffffffffu, rk[i] != 0u && rk[i] >= T));
+      for (int i = 0; i < ITEMS; ++i) mine += __popc(__ballot_sync(0xffffffffu, selected(i)));
+      __syncthreads();
       if (tid < 4) s_local[tid] = 0;
       __syncthreads();
       if (lane == 0 && mine) atomicAdd(&s_local[0], mine);
@@ -394,69 +410,59 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
-      const u32 key = rk[i];
-      const bool sel = key != 0u && key >= T;
+      const bool sel = selected(i);
       const u32 m = __ballot_sync(0xffffffffu, sel);
       int base = 0;
       if (lane == 0 && m) base = atomicAdd(&s_local[0], __popc(m));
       base = __shfl_sync(0xffffffffu, base, 0);
-      if (sel) {
-        const int q = q_begin + tid + i * 1024;
-        const u32 p = (u32)q_to_p(q, hwc, dg.A);
-        L_sort[s_local[1] + base + __popc(m & ((1u << lane) - 1u))] = ((u64)key << 32) | (u32)(~p);
-      }
+      if (sel) L_sort[s_local[1] + base + __popc(m & ((1u << lane) - 1u))] = ((u64)rk[i] << 32) | (u32)(~p_of_item(i));
     }
     if (rank == 0)
-      for (int i = k1 + tid; i < n_pow2; i += blockDim.x) sortbuf[i] = 0ull;
+      for (int i = k_sel + tid; i < max(n_pow2, 1024); i += blockDim.x)
+        if (i < g.sort_cap) sortbuf[i] = 0ull;
     cluster.sync();
-    MXR_STAMP(4);
-    // ---- P4: the leader orders the head: (score desc, row index asc) -- see topk_body ----
+    MXR_STAMP(stamp);
     if (rank == 0) {
-      if (n_pow2 <= 1024) {
-        for (int i = n_pow2 + tid; i < 1024; i += blockDim.x) sortbuf[i] = 0ull;
-        __syncthreads();
-        bitonic_sort_1024_regs(sortbuf, n_pow2);
-      } else {
-        bitonic_sort_desc_u64(sortbuf, n_pow2);
-      }
+      if (n_pow2 <= 1024) bitonic_sort_1024_regs(sortbuf, n_pow2);
+      else bitonic_sort_desc_u64(sortbuf, n_pow2);
     }
     cluster.sync();
-    MXR_STAMP(5);
-    // ---- P5: all CTAs re-decode their slice of the head into processing order ----
-    {
-      const int per = (k1 + kClusterSize - 1) / kClusterSize;
-      for (int i = rank * per + tid; i < min((rank + 1) * per, k1); i += blockDim.x) {
-        const int p = (int)(~(u32)L_sort[i]);
-        const int a = p % dg.A, r = p / dg.A;
-        const int h = r / dg.wc, w = r - h * dg.wc;
-        double bx[4];
-        decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx);
-        const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
-        const float s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
-        const size_t o = (size_t)b * g.a.cap + i;
-        const_cast<double4*>(g.a.box)[o] = make_double4(bx[0], bx[1], bx[2], bx[3]);
-        const_cast<double*>(g.a.area)[o] = box_area<double>(bx[0], bx[1], bx[2], bx[3]);
-        const_cast<float*>(g.a.score)[o] = s;
-        const_cast<int*>(g.a.orig)[o] = p;
-      }
+    MXR_STAMP(stamp + 1);
+    const int per = (k_sel + kClusterSize - 1) / kClusterSize;
+    for (int i = rank * per + tid; i < min((rank + 1) * per, k_sel); i += blockDim.x) {
+      const int p = (int)(~(u32)L_sort[i]);
+      const int a = p % dg.A, r = p / dg.A;
+      const int h = r / dg.wc, w = r - h * dg.wc;
+      double bx[4];
+      decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx);
+      const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
+      const float s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
+      const size_t o = (size_t)b * g.a.cap + i;
+      const_cast<double4*>(g.a.box)[o] = make_double4(bx[0], bx[1], bx[2], bx[3]);
+      const_cast<double*>(g.a.area)[o] = box_area<double>(bx[0], bx[1], bx[2], bx[3]);
+      const_cast<float*>(g.a.score)[o] = s;
+      const_cast<int*>(g.a.orig)[o] = p;
     }
     __threadfence();
     cluster.sync();
-    MXR_STAMP(6);
-    // ---- P6: stripes of 256 boxes (cluster barriers cost ~0.2 us, so narrow stripes keep the
-    //      evaluated IoU pairs close to what the greedy walk really needs) ----
-    const double4* box = g.a.box + (size_t)b * g.a.cap;
-    const double* area = g.a.area + (size_t)b * g.a.cap;
-    int* kept_slot = g.a.kept_slot + (size_t)b * g.a.keep_cap;
-    const double thr_lo = Ar<double>::mul(g.thr, Ar<double>::band_lo()), thr_hi = Ar<double>::mul(g.thr, Ar<double>::band_hi());
-    const int nstripes = (k1 + kCW - 1) / kCW;
-    for (int s = 0; s < nstripes && !fin; ++s) {
+  };
+
+  // ---- greedy NMS over sorted positions [s_begin*256, n_sorted) in stripes of 256 boxes: cluster barriers
+  //      cost ~0.2 us, so narrow stripes keep the evaluated IoU pairs close to what the walk really needs ----
+  const double4* box = g.a.box + (size_t)b * g.a.cap;
+  const double* area = g.a.area + (size_t)b * g.a.cap;
+  int* kept_slot = g.a.kept_slot + (size_t)b * g.a.keep_cap;
+  const double thr_lo = Ar<double>::mul(g.thr, Ar<double>::band_lo()), thr_hi = Ar<double>::mul(g.thr, Ar<double>::band_hi());
+  int nk = 0, fin = 0, stripes_done = 0;
+  auto walk_stripes = [&](int s_begin, int n_sorted) {
+    const int nstripes = (n_sorted + kCW - 1) / kCW;
+    for (int s = s_begin; s < nstripes && !fin; ++s) {
       const int c0 = s * kCW;
-      const int c1 = min(c0 + kCW, k1);
+      const int c1 = min(c0 + kCW, n_sorted);
       {
-        // one warp per task: 32 rows x 16 columns
+        // one warp per task (32 rows x 16 columns); task u runs on CTA u % 8, warp u / 8, so that a stripe's
+        // few dozen tasks spread over all 8 SMs' FP64 pipes
         const int tp = kCTriTasks + 16 * ((nk + 31) / 32);
-        // task u runs on CTA u % 8, warp u / 8: a stripe's few dozen tasks spread over all 8 SMs' FP64 pipes
         for (int u = warp * kClusterSize + rank; u < tp; u += kClusterSize * 32) {
           int cb, qd, rb = 0, half = 0, rc = 0;
           const bool tri = u < kCTriTasks;
@@ -506,9 +512,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
           }
         }
       }
-      if (s == 0) MXR_STAMP(10);
       cluster.sync();
-      if (s == 0) MXR_STAMP(11);
       if (rank == 0) {
         int f = 0;
         nk = scan_rows_smem(sM, kCPitch, s_removed, c1 - c0, c0, nk, g.max_keep, kept_slot, &s_keptbits, &s_finish, &f);
@@ -519,9 +523,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
         }
         __threadfence();
       }
-      if (s == 0) MXR_STAMP(12);
       cluster.sync();
-      if (s == 0) MXR_STAMP(13);
       if (tid == 0) {
         s_local[2] = L_status[0];
         s_local[3] = L_status[1];
@@ -532,30 +534,60 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       stripes_done = s + 1;
       __syncthreads();
     }
+  };
+
+  // ---- head: select + sort + walk the first k1 candidates ----
+  bool head_ok = false;
+  if (k1 > 0) {
+    u64 T = 1ull << 32;  // every valid composite
+    head_ok = (k1 == n_valid) ? true : cluster_select(k1, 0, false, &T);
+    MXR_STAMP(3);
+    if (head_ok) {
+      sort_and_redecode(k1, T, 4);
+      MXR_STAMP(6);
+      walk_stripes(0, k1);
+    }
+  }
+  // ---- full list, only if the head did not settle the image ----
+  int full_path = 0;
+  if (k > 0 && !fin && (!head_ok || k1 < k)) {
+    full_path = 1;
+    u64 T = 1ull << 32;
+    if (k < n_valid) cluster_select(k, 4, true, &T);
+    sort_and_redecode(k, T, 10);
+    if (!head_ok) {
+      nk = 0;            // nothing was walked (a run of equal scores is cut by the head boundary)
+      stripes_done = 0;
+    }
+    walk_stripes(stripes_done, k);
   }
   MXR_STAMP(7);
-  // ---- P7: results, or hand-over state for the general path ----
+  if (!head_ok && g.dbg && rank == 0 && tid == 0)
+    for (int i = 3; i <= 6; ++i) g.dbg[(size_t)b * 16 + i] = g.dbg[(size_t)b * 16 + 2];  // head phases did not run
+  // ---- results (proposal.py:140-149) ----
   if (rank == 0) {
-    const bool finished = !bail && (fin || k1 >= k);
     Ctrl* cb = g.ctrl + b;
     if (tid == 0) {
       cb->n_valid = n_valid;
       cb->nan_flag = nan_flag;
       cb->n = k;
       cb->nkept = nk;
-      cb->done = finished ? 1 : 0;
-      cb->pad[0] = bail ? 0 : (stripes_done * kCW) / kCoopW;   // first 1024-box stripe the general path still has to walk
+      cb->done = 1;
+      cb->pad[0] = 0;
     }
     __syncthreads();
-    if (finished) coop_write_outputs<double>(g.a, g.o, cb, b, nk, k);
+    coop_write_outputs<double>(g.a, g.o, cb, b, nk, k);
   }
   cluster.sync();  // nobody leaves while its shared memory may still be addressed
   MXR_STAMP(8);
-  if (g.dbg && rank == 0 && tid == 0) g.dbg[(size_t)b * 16 + 9] = (u64)stripes_done;
+  if (g.dbg && rank == 0 && tid == 0) {
+    g.dbg[(size_t)b * 16 + 9] = (u64)stripes_done;
+    g.dbg[(size_t)b * 16 + 14] = (u64)full_path;
+  }
 }
 
-static inline size_t cluster_smem_bytes() {
-  return (size_t)kSortMax * 8 + (size_t)kCW * kCPitch * 8 + 8 * 8 + 32 * 16 * (sizeof(double4) + sizeof(double)) + 256;
+static inline size_t cluster_smem_bytes(int sort_cap) {
+  return (size_t)sort_cap * 8 + (size_t)kCW * kCPitch * 8 + 8 * 8 + 32 * 16 * (sizeof(double4) + sizeof(double)) + 256;
 }
 
 }  // namespace mxr
