@@ -443,8 +443,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       const_cast<float*>(g.a.score)[o] = s;
       const_cast<int*>(g.a.orig)[o] = p;
     }
-    __threadfence();
-    cluster.sync();
+    cluster.sync();  // release/acquire at cluster scope: the boxes are visible to every CTA of the cluster
   };
 
   // ---- greedy NMS over sorted positions [s_begin*256, n_sorted) in stripes of 256 boxes: cluster barriers
@@ -521,7 +520,6 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
           s_status[0] = nk;
           s_status[1] = f;
         }
-        __threadfence();
       }
       cluster.sync();
       if (tid == 0) {
