@@ -144,7 +144,7 @@ const char* mxr_profile_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"memset",          "decode_filter_kernel", "topk_sort_kernel", "nms_stripe_kernel",
                                         "nms_scan_kernel", "nms_prepare_kernel",   "boxes_kernels",    "overlaps_kernels",
                                         "anchor_target_kernels", "proposal_target_kernels", "nms_coop_kernel",
-                                        "proposal_cluster_kernel"};
+                                        "proposal_cluster_kernel", "nms_cluster_kernel"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 
@@ -169,7 +169,6 @@ int mxr_proposal_phase_times(mxr_handle_t hh, int max_images, double* us_out, in
   for (int b = 0; b < n; ++b) {
     for (int i = 0; i < 8; ++i) us_out[b * 9 + i] = (double)(tmp[b * 16 + i + 1] - tmp[b * 16 + i]) * 1e-3;
     us_out[b * 9 + 8] = (double)tmp[b * 16 + 9];
-    if (getenv("MXR_DEBUG_STRIPE")) fprintf(stderr, "[stripe0 img %d] tiles %.2f sync %.2f scan %.2f sync %.2f us\n", b, (tmp[b*16+10]-tmp[b*16+6])*1e-3, (tmp[b*16+11]-tmp[b*16+10])*1e-3, (tmp[b*16+12]-tmp[b*16+11])*1e-3, (tmp[b*16+13]-tmp[b*16+12])*1e-3);
   }
   delete[] tmp;
   *images_out = n;

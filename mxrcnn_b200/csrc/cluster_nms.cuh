@@ -1,0 +1,267 @@
+// Greedy NMS inside one thread-block cluster (shared by the fused proposal kernel and the generic
+// nms kernel): boxes already in processing order in global memory, bit rows and suppression words in
+// the leader CTA's shared memory, reached from the other CTAs through distributed shared memory.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "device_math.cuh"
+
+namespace mxr {
+
+static const int kCW = 256;        // stripe width (cluster barriers are cheap, so stripes are narrow)
+static const int kCSW = 4;         // 64-bit words per stripe row
+static const int kCPitch = 5;      // shared-memory row pitch in words
+static const int kCTriTasks = 80;  // 10 lower-triangle tiles x 2 row halves x 4 column quarters
+
+template <typename T>
+__device__ __forceinline__ typename Ar<T>::Box ldcg_box(const typename Ar<T>::Box* p);
+template <>
+__device__ __forceinline__ double4 ldcg_box<double>(const double4* p) {
+  const double2 a = __ldcg(reinterpret_cast<const double2*>(p));
+  const double2 b = __ldcg(reinterpret_cast<const double2*>(p) + 1);
+  return make_double4(a.x, a.y, b.x, b.y);
+}
+template <>
+__device__ __forceinline__ float4 ldcg_box<float>(const float4* p) {
+  return __ldcg(p);
+}
+
+// Descending bitonic sort of n_pow2 <= 1024 distinct 64-bit keys, one key per thread (blockDim.x == 1024):
+// strides below 32 are warp shuffles, only strides >= 32 go through shared memory (15 of the 55 stages).
+__device__ __forceinline__ void bitonic_sort_1024_regs(u64* buf, int n_pow2) {
+  const int t = threadIdx.x;
+  u64 v = buf[t];  // entries beyond the real keys are zero-padded by the caller up to 1024
+  for (int size = 2; size <= n_pow2; size <<= 1) {
+    const bool desc = (t & size) == 0;
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      u64 other;
+      if (stride < 32) {
+        other = __shfl_xor_sync(0xffffffffu, v, stride);
+      } else {
+        __syncthreads();
+        buf[t] = v;
+        __syncthreads();
+        other = buf[t ^ stride];
+      }
+      const bool lower = (t & stride) == 0;
+      const bool take_max = (lower == desc);
+      const bool other_gt = other > v;
+      v = (take_max == other_gt) ? other : v;
+    }
+  }
+  __syncthreads();
+  buf[t] = v;
+  __syncthreads();
+}
+
+// 16 columns of one row: bit j set when column j is suppressed by the row box (nms.py:25-36).
+template <typename T>
+__device__ __forceinline__ u32 tile_bits16(const typename Ar<T>::Box rb, T rarea, const typename Ar<T>::Box* cols,
+                                           const T* careas, int j_begin, int j_end, T thr, T thr_lo, T thr_hi) {
+  u32 bits = 0;
+  if (thr > T(0)) {
+#pragma unroll 4
+    for (int j = j_begin; j < j_end; ++j) {
+      const typename Ar<T>::Box cb = cols[j];
+      int r = iou_band<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr_lo, thr_hi);
+      if (r == 2) r = iou_exceeds<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr) ? 1 : 0;
+      bits |= (u32)r << j;
+    }
+  } else {
+    for (int j = j_begin; j < j_end; ++j) {
+      const typename Ar<T>::Box cb = cols[j];
+      if (iou_exceeds<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr)) bits |= 1u << j;
+    }
+  }
+  return bits;
+}
+
+// Greedy walk of one stripe whose bit rows already sit in shared memory.  Whole CTA.
+// Diagonal tiles hold their LOWER triangle (bit j of row i, j < i: "j suppresses i"; the IoU predicate is
+// symmetric bit for bit), off-diagonal words hold "row suppresses column".
+// Returns the new kept count; *fin_out != 0 when the quota was reached.
+__device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_removed, int rows, int c0, int nk, int max_keep,
+                                              int* kept_slot, u64* s_keptbits, int* s_finish, int* fin_out) {
+  const int tid = threadIdx.x;
+  const int nblk = (rows + 63) >> 6;
+  int finished = 0;
+  for (int blk = 0; blk < nblk; ++blk) {
+    __syncthreads();
+    if (tid < 32) {
+      const u64 word0 = s_removed[blk];
+      const int nvalid = min(64, rows - blk * 64);
+      const u64 valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1ull);
+      const u64 alive = ~word0 & valid;
+      // Greedy keep is the unique fixed point of  keep_i = alive_i and no kept j < i suppresses i ;
+      // iterating from keep = alive fixes at least one more leading position per round, and in practice
+      // converges in a handful of rounds instead of a 64-step dependent chain.
+      const u64 m0 = ((blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * pitch + blk] : 0ull) & ((1ull << tid) - 1ull);
+      const u64 m1 = ((blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * pitch + blk] : 0ull) & ((1ull << (tid + 32)) - 1ull);
+      const bool a0 = (alive >> tid) & 1ull, a1 = (alive >> (tid + 32)) & 1ull;
+      u64 keep = alive;
+      for (int it = 0; it < 64; ++it) {
+        const u32 k0 = __ballot_sync(0xffffffffu, a0 && (m0 & keep) == 0ull);
+        const u32 k1 = __ballot_sync(0xffffffffu, a1 && (m1 & keep) == 0ull);
+        const u64 nxt = ((u64)k1 << 32) | k0;
+        if (nxt == keep) break;
+        keep = nxt;
+      }
+      u64 kept = keep;
+      int fin = 0;
+      if (max_keep > 0 && nk + __popcll(kept) >= max_keep) {
+        int want = max_keep - nk;
+        u64 k2 = 0, rest = kept;
+        while (want > 0 && rest) {
+          const u64 low = rest & (~rest + 1ull);
+          k2 |= low;
+          rest ^= low;
+          --want;
+        }
+        kept = k2;
+        fin = 1;
+      }
+      if (tid == 0) {
+        *s_keptbits = kept;
+        *s_finish = fin;
+      }
+    }
+    __syncthreads();
+    const u64 kept = *s_keptbits;
+    const int fin = *s_finish;
+    if (tid < 64 && ((kept >> tid) & 1ull)) kept_slot[nk + __popcll(kept & ((1ull << tid) - 1ull))] = c0 + blk * 64 + tid;
+    nk += __popcll(kept);
+    if (fin) {
+      finished = 1;
+      break;
+    }
+    const int nw = nblk - blk - 1;
+    const int w = tid >> 6, row = tid & 63;
+    if (w < nw) {
+      const u64 v = ((kept >> row) & 1ull) ? sM[(blk * 64 + row) * pitch + blk + 1 + w] : 0ull;
+      const u32 vlo = __reduce_or_sync(0xffffffffu, (u32)v);
+      const u32 vhi = __reduce_or_sync(0xffffffffu, (u32)(v >> 32));
+      if ((tid & 31) == 0 && (vlo | vhi)) atomicOr(&s_removed[blk + 1 + w], ((u64)vhi << 32) | vlo);
+    }
+  }
+  __syncthreads();
+  *fin_out = finished;
+  return nk;
+}
+
+// Everything the stripe walk needs; all shared-memory pointers are this CTA's own copies, the L_* ones
+// address the leader (rank 0) through DSMEM.
+template <typename T>
+struct StripeWalker {
+  const typename Ar<T>::Box* box;   // [n] processing order, global
+  const T* area;
+  int* kept_slot;                   // global, kept boxes so far
+  u64* sM;                          // leader smem: [kCW][kCPitch]
+  u64* s_removed;                   // leader smem: [kCSW]
+  int* s_status;                    // leader smem: [2] kept so far, quota reached
+  u64* L_sM;
+  u64* L_removed;
+  int* L_status;
+  typename Ar<T>::Box* t_box;       // this warp's staging: [16]
+  T* t_area;
+  u64* s_keptbits;
+  int* s_finish;
+  int* s_local;                     // [4] scratch of this CTA
+  T thr;
+  int max_keep;
+  // walk state (identical in every thread of the cluster)
+  int nk, fin, stripes_done;
+
+  template <typename Cluster>
+  __device__ __forceinline__ void walk(Cluster& cluster, int s_begin, int n_sorted) {
+    const int rank = (int)cluster.block_rank();
+    const int csize = (int)cluster.num_blocks();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const T thr_lo = Ar<T>::mul(thr, Ar<T>::band_lo()), thr_hi = Ar<T>::mul(thr, Ar<T>::band_hi());
+    const int nstripes = (n_sorted + kCW - 1) / kCW;
+    for (int s = s_begin; s < nstripes && !fin; ++s) {
+      const int c0 = s * kCW;
+      const int c1 = min(c0 + kCW, n_sorted);
+      {
+        // one warp per task (32 rows x 16 columns); task u runs on CTA u % csize, warp u / csize, so that a
+        // stripe's few dozen tasks spread over all the cluster's SMs
+        const int tp = kCTriTasks + 16 * ((nk + 31) / 32);
+        for (int u = warp * csize + rank; u < tp; u += csize * 32) {
+          int cb, qd, rb = 0, half = 0, rc = 0;
+          const bool tri = u < kCTriTasks;
+          if (tri) {
+            int t = u >> 3;
+            half = (u >> 2) & 1;
+            qd = u & 3;
+            while (t >= kCSW - rb) {
+              t -= kCSW - rb;
+              ++rb;
+            }
+            cb = rb + t;
+          } else {
+            const int v = u - kCTriTasks;
+            qd = v & 3;
+            cb = (v >> 2) & 3;
+            rc = v >> 4;
+          }
+          const int col0 = c0 + cb * 64 + qd * 16;
+          if (col0 >= c1) continue;
+          const int ncols = min(16, c1 - col0);
+          __syncwarp();
+          if (lane < ncols) {
+            t_box[lane] = ldcg_box<T>(box + col0 + lane);
+            t_area[lane] = __ldcg(area + col0 + lane);
+          }
+          __syncwarp();
+          if (tri) {
+            const int rt = half * 32 + lane;           // row inside the 64x64 tile
+            const int rl = rb * 64 + rt;               // row inside the stripe
+            const int row = c0 + rl;
+            if (row < c1) {
+              int je = ncols;
+              if (rb == cb) je = min(ncols, max(0, rt - qd * 16));   // diagonal tile: strictly BELOW the diagonal
+              const u32 bits = tile_bits16<T>(ldcg_box<T>(box + row), __ldcg(area + row), t_box, t_area, 0, je, thr, thr_lo, thr_hi);
+              reinterpret_cast<unsigned short*>(L_sM + rl * kCPitch + cb)[qd] = (unsigned short)bits;
+            }
+          } else {
+            u32 bits = 0;
+            const int kidx = rc * 32 + lane;
+            if (kidx < nk) {
+              const int slot = __ldcg(kept_slot + kidx);
+              bits = tile_bits16<T>(ldcg_box<T>(box + slot), __ldcg(area + slot), t_box, t_area, 0, ncols, thr, thr_lo, thr_hi);
+            }
+            bits = __reduce_or_sync(0xffffffffu, bits);
+            if (lane == 0 && bits) atomicOr(reinterpret_cast<u32*>(L_removed + cb) + (qd >> 1), bits << (16 * (qd & 1)));
+          }
+        }
+      }
+      cluster.sync();
+      if (rank == 0) {
+        int f = 0;
+        nk = scan_rows_smem(sM, kCPitch, s_removed, c1 - c0, c0, nk, max_keep, kept_slot, s_keptbits, s_finish, &f);
+        if (tid < kCSW) s_removed[tid] = 0ull;
+        if (tid == 0) {
+          s_status[0] = nk;
+          s_status[1] = f;
+        }
+      }
+      cluster.sync();
+      if (tid == 0) {
+        s_local[2] = L_status[0];
+        s_local[3] = L_status[1];
+      }
+      __syncthreads();
+      nk = s_local[2];
+      fin = s_local[3];
+      stripes_done = s + 1;
+      __syncthreads();
+    }
+  }
+};
+
+// bytes of dynamic shared memory after the sort buffer: bit rows + suppression words + per-warp staging
+template <typename T>
+static inline size_t cluster_nms_smem_bytes() {
+  return (size_t)kCW * kCPitch * 8 + 8 * 8 + 32 * 16 * (sizeof(typename Ar<T>::Box) + sizeof(T)) + 256;
+}
+
+}  // namespace mxr

@@ -68,7 +68,8 @@ enum Stage {
   ST_PROPOSAL_TARGET = 9,
   ST_NMS_COOP = 10,
   ST_CLUSTER = 11,
-  ST_COUNT = 12
+  ST_NMS_CLUSTER = 12,
+  ST_COUNT = 13
 };
 
 struct ProfRec {

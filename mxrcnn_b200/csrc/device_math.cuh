@@ -77,17 +77,17 @@ __device__ __forceinline__ bool iou_exceeds(T ax1, T ay1, T ax2, T ay2, T aarea,
 // (thr > 0 checked by the caller; the extra rounding of the hoisted products is < 2^-52, far inside
 // the 2^-48 band).  Returns 0 = keep, 1 = suppressed, 2 = inside the band / degenerate: the caller
 // re-evaluates with iou_exceeds().  Branch-free so that a warp does not diverge on it.
-__device__ __forceinline__ int iou_band_f64(double ax1, double ay1, double ax2, double ay2, double aarea, double bx1,
-                                            double by1, double bx2, double by2, double barea, double thr_lo,
-                                            double thr_hi) {
-  typedef Ar<double> A;
-  const double xx1 = A::vmax(ax1, bx1), yy1 = A::vmax(ay1, by1);
-  const double xx2 = A::vmin(ax2, bx2), yy2 = A::vmin(ay2, by2);
-  const double w0 = A::add(A::sub(xx2, xx1), 1.0), h0 = A::add(A::sub(yy2, yy1), 1.0);
-  const double w = w0 > 0.0 ? w0 : 0.0, h = h0 > 0.0 ? h0 : 0.0;
-  const double inter = A::mul(w, h);
-  const double uni = A::sub(A::add(aarea, barea), inter);
-  const bool pos = uni > 0.0;
+template <typename T>
+__device__ __forceinline__ int iou_band(T ax1, T ay1, T ax2, T ay2, T aarea, T bx1, T by1, T bx2, T by2, T barea, T thr_lo,
+                                        T thr_hi) {
+  typedef Ar<T> A;
+  const T xx1 = A::vmax(ax1, bx1), yy1 = A::vmax(ay1, by1);
+  const T xx2 = A::vmin(ax2, bx2), yy2 = A::vmin(ay2, by2);
+  const T w0 = A::add(A::sub(xx2, xx1), T(1)), h0 = A::add(A::sub(yy2, yy1), T(1));
+  const T w = w0 > T(0) ? w0 : T(0), h = h0 > T(0) ? h0 : T(0);
+  const T inter = A::mul(w, h);
+  const T uni = A::sub(A::add(aarea, barea), inter);
+  const bool pos = uni > T(0);
   const bool keep = inter <= A::mul(thr_lo, uni);
   const bool supp = inter >= A::mul(thr_hi, uni);
   return !pos ? 2 : (keep ? 0 : (supp ? 1 : 2));

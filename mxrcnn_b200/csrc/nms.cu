@@ -1,6 +1,7 @@
 // helper/processing/nms.py:4-38 -- nms(dets, thresh), single and batched (per-class) forms.
 #include <string.h>
 
+#include "nms_cluster.cuh"
 #include "nms_host.cuh"
 #include "sort.cuh"
 
@@ -182,6 +183,63 @@ int enqueue_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets, doub
   return run_nms_stripes<T>(h, s, L.ctrl, na, o, L.P, L.n_max, max_keep > 0 ? L.keep_cap : 0, L.plan, (T)thresh);
 }
 
+// One launch of nms_cluster_kernel: a cluster of 2, 4 or 8 CTAs per problem.
+template <typename T>
+int enqueue_cluster_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets, double thresh, int max_keep,
+                      int32_t* keep_out, int32_t* nkeep_out) {
+  NmsClusterArgs<T> g;
+  g.dets = dets;
+  g.offsets = L.offsets;
+  g.a.box = reinterpret_cast<typename Ar<T>::Box*>(L.box);
+  g.a.area = reinterpret_cast<T*>(L.area);
+  g.a.score = nullptr;
+  g.a.orig = L.orig;
+  g.a.cap = L.cap;
+  g.a.M = nullptr;
+  g.a.m_pitch = 0;
+  g.a.m_stride = 0;
+  g.a.R = nullptr;
+  g.a.r_words = 0;
+  g.a.kept_slot = L.kept_slot;
+  g.a.keep_cap = L.keep_cap;
+  g.o.rois = nullptr;
+  g.o.scores = nullptr;
+  g.o.keep_pos = nullptr;
+  g.o.keep_orig = keep_out;
+  g.o.nkeep = nkeep_out;
+  g.o.rows = 0;
+  g.o.row_offsets = L.offsets;
+  g.ctrl = L.ctrl;
+  g.thr = (T)thresh;  // compared in the dtype of dets, like numpy (see enqueue_t)
+  g.max_keep = max_keep > 0 ? L.keep_cap : 0;
+  g.sort_cap = L.n_pow2_max < 1024 ? 1024 : L.n_pow2_max;
+  const size_t smem = nms_cluster_smem_bytes<T>(g.sort_cap);
+  const int slot = sizeof(T) == 8 ? 7 : 6;
+  if ((int)smem > h->smem_attr[slot]) {
+    MXR_CUDA(cudaFuncSetAttribute(nms_cluster_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    h->smem_attr[slot] = (int)smem;
+  }
+  const int csize = L.n_max > 1024 ? 8 : (L.n_max > 256 ? 4 : 2);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(L.P * csize);
+  cfg.blockDim = dim3(1024);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = csize;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  prof_begin(h, s, ST_NMS_CLUSTER);
+  MXR_CUDA(cudaLaunchKernelEx(&cfg, nms_cluster_kernel<T>, g));
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
 // offsets: HOST array of P+1 ints.
 int run(Handle* h, cudaStream_t s, const void* dets, bool dets_on_host, const int32_t* offsets, int P, int dtype,
         double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out) {
@@ -218,10 +276,18 @@ int run(Handle* h, cudaStream_t s, const void* dets, bool dets_on_host, const in
     d_keep = L.d_keep;
     d_nkeep = L.d_nkeep;
   }
+  // one cluster launch when a problem's sort fits the leader's shared memory, else the striped kernels
+  const bool use_cluster = !h->no_cluster && n_max <= (dtype == MXR_DTYPE_F64 ? 8192 : 16384);
   if (dtype == MXR_DTYPE_F64) {
-    MXR_TRY(enqueue_t<double>(h, s, L, reinterpret_cast<const double*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+    if (use_cluster)
+      MXR_TRY(enqueue_cluster_t<double>(h, s, L, reinterpret_cast<const double*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+    else
+      MXR_TRY(enqueue_t<double>(h, s, L, reinterpret_cast<const double*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
   } else {
-    MXR_TRY(enqueue_t<float>(h, s, L, reinterpret_cast<const float*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+    if (use_cluster)
+      MXR_TRY(enqueue_cluster_t<float>(h, s, L, reinterpret_cast<const float*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+    else
+      MXR_TRY(enqueue_t<float>(h, s, L, reinterpret_cast<const float*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
   }
   if (dets_on_host) {
     char* hp = h->h_pin + off_bytes;

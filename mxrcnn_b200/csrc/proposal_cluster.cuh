@@ -18,16 +18,13 @@
 #pragma once
 #include <cooperative_groups.h>
 
+#include "cluster_nms.cuh"
 #include "nms_coop.cuh"
 #include "proposal_kernels.cuh"
 
 namespace mxr {
 
 static const int kClusterSize = 8;
-static const int kCW = 256;        // stripe width inside the cluster kernel (cluster barriers are cheap)
-static const int kCSW = 4;         // words per stripe row
-static const int kCPitch = 5;      // shared-memory row pitch in words
-static const int kCTriTasks = 80;  // 10 upper-triangle tiles x 2 row halves x 4 column quarters
 static const int kClusterSortMax = 16384;  // largest list the leader sorts in shared memory (128 KiB)
 
 struct ClusterArgs {
@@ -58,138 +55,11 @@ __device__ __forceinline__ u64 global_ns() {
     if (g.dbg && rank == 0 && tid == 0) g.dbg[(size_t)b * 16 + (i)] = global_ns(); \
   } while (0)
 
-__device__ __forceinline__ double4 ldcg_box(const double4* p) {
-  const double2 a = __ldcg(reinterpret_cast<const double2*>(p));
-  const double2 b = __ldcg(reinterpret_cast<const double2*>(p) + 1);
-  return make_double4(a.x, a.y, b.x, b.y);
-}
-
 __device__ __forceinline__ void remote_or64(u64* p, u64 v) {
   u32* q = reinterpret_cast<u32*>(p);
   const u32 lo = (u32)v, hi = (u32)(v >> 32);
   if (lo) atomicOr(q, lo);
   if (hi) atomicOr(q + 1, hi);
-}
-
-// Descending bitonic sort of n_pow2 <= 1024 distinct 64-bit keys, one key per thread (blockDim.x == 1024):
-// strides below 32 are warp shuffles, only strides >= 32 go through shared memory (15 of the 55 stages).
-__device__ __forceinline__ void bitonic_sort_1024_regs(u64* buf, int n_pow2) {
-  const int t = threadIdx.x;
-  u64 v = buf[t];  // entries beyond the real keys are zero-padded by the caller up to n_pow2; beyond that unused
-  for (int size = 2; size <= n_pow2; size <<= 1) {
-    const bool desc = (t & size) == 0;
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      u64 other;
-      if (stride < 32) {
-        other = __shfl_xor_sync(0xffffffffu, v, stride);
-      } else {
-        __syncthreads();
-        buf[t] = v;
-        __syncthreads();
-        other = buf[t ^ stride];
-      }
-      const bool lower = (t & stride) == 0;
-      const bool take_max = (lower == desc);
-      const bool other_gt = other > v;
-      v = (take_max == other_gt) ? other : v;
-    }
-  }
-  __syncthreads();
-  buf[t] = v;
-  __syncthreads();
-}
-
-// 16 columns of one row: bit j set when column j is suppressed by the row box (nms.py:25-36).
-__device__ __forceinline__ u32 tile_bits16(const double4 rb, double rarea, const double4* cols, const double* careas,
-                                           int j_begin, int j_end, double thr, double thr_lo, double thr_hi) {
-  u32 bits = 0;
-  if (thr > 0.0) {
-#pragma unroll 4
-    for (int j = j_begin; j < j_end; ++j) {
-      const double4 cb = cols[j];
-      int r = iou_band_f64(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr_lo, thr_hi);
-      if (r == 2) r = iou_exceeds<double>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr) ? 1 : 0;
-      bits |= (u32)r << j;
-    }
-  } else {
-    for (int j = j_begin; j < j_end; ++j) {
-      const double4 cb = cols[j];
-      if (iou_exceeds<double>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr)) bits |= 1u << j;
-    }
-  }
-  return bits;
-}
-
-// Greedy walk of one stripe whose bit rows already sit in shared memory (pitch kCoopPitch).
-// Whole CTA.  Returns the new kept count; *fin_out != 0 when the quota was reached.
-__device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_removed, int rows, int c0, int nk, int max_keep,
-                                              int* kept_slot, u64* s_keptbits, int* s_finish, int* fin_out) {
-  const int tid = threadIdx.x;
-  const int nblk = (rows + 63) >> 6;
-  int finished = 0;
-  for (int blk = 0; blk < nblk; ++blk) {
-    __syncthreads();
-    if (tid < 32) {
-      const u64 word0 = s_removed[blk];
-      const int nvalid = min(64, rows - blk * 64);
-      const u64 valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1ull);
-      const u64 alive = ~word0 & valid;
-      // Diagonal tile, stored as its LOWER triangle: bit j of row i (j < i) says "j suppresses i" (the IoU
-      // predicate is symmetric bit for bit).  Greedy keep is the unique fixed point of
-      //   keep_i = alive_i and no kept j < i suppresses i ;
-      // iterating from keep = alive fixes at least one more leading position per round, and in practice
-      // converges in a handful of rounds instead of a 64-step dependent chain.
-      const u64 m0 = ((blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * pitch + blk] : 0ull) & ((1ull << tid) - 1ull);
-      const u64 m1 = ((blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * pitch + blk] : 0ull) & ((1ull << (tid + 32)) - 1ull);
-      const bool a0 = (alive >> tid) & 1ull, a1 = (alive >> (tid + 32)) & 1ull;
-      u64 keep = alive;
-      for (int it = 0; it < 64; ++it) {
-        const u32 k0 = __ballot_sync(0xffffffffu, a0 && (m0 & keep) == 0ull);
-        const u32 k1 = __ballot_sync(0xffffffffu, a1 && (m1 & keep) == 0ull);
-        const u64 nxt = ((u64)k1 << 32) | k0;
-        if (nxt == keep) break;
-        keep = nxt;
-      }
-      u64 kept = keep;
-      int fin = 0;
-      if (max_keep > 0 && nk + __popcll(kept) >= max_keep) {
-        int want = max_keep - nk;
-        u64 k2 = 0, rest = kept;
-        while (want > 0 && rest) {
-          const u64 low = rest & (~rest + 1ull);
-          k2 |= low;
-          rest ^= low;
-          --want;
-        }
-        kept = k2;
-        fin = 1;
-      }
-      if (tid == 0) {
-        *s_keptbits = kept;
-        *s_finish = fin;
-      }
-    }
-    __syncthreads();
-    const u64 kept = *s_keptbits;
-    const int fin = *s_finish;
-    if (tid < 64 && ((kept >> tid) & 1ull)) kept_slot[nk + __popcll(kept & ((1ull << tid) - 1ull))] = c0 + blk * 64 + tid;
-    nk += __popcll(kept);
-    if (fin) {
-      finished = 1;
-      break;
-    }
-    const int nw = nblk - blk - 1;
-    const int w = tid >> 6, row = tid & 63;
-    if (w < nw) {
-      const u64 v = ((kept >> row) & 1ull) ? sM[(blk * 64 + row) * pitch + blk + 1 + w] : 0ull;
-      const u32 vlo = __reduce_or_sync(0xffffffffu, (u32)v);
-      const u32 vhi = __reduce_or_sync(0xffffffffu, (u32)(v >> 32));
-      if ((tid & 31) == 0 && (vlo | vhi)) atomicOr(&s_removed[blk + 1 + w], ((u64)vhi << 32) | vlo);
-    }
-  }
-  __syncthreads();
-  *fin_out = finished;
-  return nk;
 }
 
 // grid B * kClusterSize CTAs, cluster (kClusterSize,1,1), block 1024.
@@ -446,93 +316,27 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     cluster.sync();  // release/acquire at cluster scope: the boxes are visible to every CTA of the cluster
   };
 
-  // ---- greedy NMS over sorted positions [s_begin*256, n_sorted) in stripes of 256 boxes: cluster barriers
-  //      cost ~0.2 us, so narrow stripes keep the evaluated IoU pairs close to what the walk really needs ----
-  const double4* box = g.a.box + (size_t)b * g.a.cap;
-  const double* area = g.a.area + (size_t)b * g.a.cap;
-  int* kept_slot = g.a.kept_slot + (size_t)b * g.a.keep_cap;
-  const double thr_lo = Ar<double>::mul(g.thr, Ar<double>::band_lo()), thr_hi = Ar<double>::mul(g.thr, Ar<double>::band_hi());
-  int nk = 0, fin = 0, stripes_done = 0;
-  auto walk_stripes = [&](int s_begin, int n_sorted) {
-    const int nstripes = (n_sorted + kCW - 1) / kCW;
-    for (int s = s_begin; s < nstripes && !fin; ++s) {
-      const int c0 = s * kCW;
-      const int c1 = min(c0 + kCW, n_sorted);
-      {
-        // one warp per task (32 rows x 16 columns); task u runs on CTA u % 8, warp u / 8, so that a stripe's
-        // few dozen tasks spread over all 8 SMs' FP64 pipes
-        const int tp = kCTriTasks + 16 * ((nk + 31) / 32);
-        for (int u = warp * kClusterSize + rank; u < tp; u += kClusterSize * 32) {
-          int cb, qd, rb = 0, half = 0, rc = 0;
-          const bool tri = u < kCTriTasks;
-          if (tri) {
-            int t = u >> 3;
-            half = (u >> 2) & 1;
-            qd = u & 3;
-            while (t >= kCSW - rb) {
-              t -= kCSW - rb;
-              ++rb;
-            }
-            cb = rb + t;
-          } else {
-            const int v = u - kCTriTasks;
-            qd = v & 3;
-            cb = (v >> 2) & 3;
-            rc = v >> 4;
-          }
-          const int col0 = c0 + cb * 64 + qd * 16;
-          if (col0 >= c1) continue;
-          const int ncols = min(16, c1 - col0);
-          __syncwarp();
-          if (lane < ncols) {
-            t_box[lane] = ldcg_box(box + col0 + lane);
-            t_area[lane] = __ldcg(area + col0 + lane);
-          }
-          __syncwarp();
-          if (tri) {
-            const int rt = half * 32 + lane;           // row inside the 64x64 tile
-            const int rl = rb * 64 + rt;               // row inside the stripe
-            const int row = c0 + rl;
-            if (row < c1) {
-              int je = ncols;
-              if (rb == cb) je = min(ncols, max(0, rt - qd * 16));   // diagonal tile: strictly BELOW the diagonal
-              const u32 bits = tile_bits16(ldcg_box(box + row), __ldcg(area + row), t_box, t_area, 0, je, g.thr, thr_lo, thr_hi);
-              reinterpret_cast<unsigned short*>(L_sM + rl * kCPitch + cb)[qd] = (unsigned short)bits;
-            }
-          } else {
-            u32 bits = 0;
-            const int kidx = rc * 32 + lane;
-            if (kidx < nk) {
-              const int slot = __ldcg(kept_slot + kidx);
-              bits = tile_bits16(ldcg_box(box + slot), __ldcg(area + slot), t_box, t_area, 0, ncols, g.thr, thr_lo, thr_hi);
-            }
-            bits = __reduce_or_sync(0xffffffffu, bits);
-            if (lane == 0 && bits) atomicOr(reinterpret_cast<u32*>(L_removed + cb) + (qd >> 1), bits << (16 * (qd & 1)));
-          }
-        }
-      }
-      cluster.sync();
-      if (rank == 0) {
-        int f = 0;
-        nk = scan_rows_smem(sM, kCPitch, s_removed, c1 - c0, c0, nk, g.max_keep, kept_slot, &s_keptbits, &s_finish, &f);
-        if (tid < kCSW) s_removed[tid] = 0ull;
-        if (tid == 0) {
-          s_status[0] = nk;
-          s_status[1] = f;
-        }
-      }
-      cluster.sync();
-      if (tid == 0) {
-        s_local[2] = L_status[0];
-        s_local[3] = L_status[1];
-      }
-      __syncthreads();
-      nk = s_local[2];
-      fin = s_local[3];
-      stripes_done = s + 1;
-      __syncthreads();
-    }
-  };
+  // ---- greedy NMS over the sorted positions, in stripes of 256 boxes (cluster_nms.cuh) ----
+  StripeWalker<double> wk;
+  wk.box = g.a.box + (size_t)b * g.a.cap;
+  wk.area = g.a.area + (size_t)b * g.a.cap;
+  wk.kept_slot = g.a.kept_slot + (size_t)b * g.a.keep_cap;
+  wk.sM = sM;
+  wk.s_removed = s_removed;
+  wk.s_status = s_status;
+  wk.L_sM = L_sM;
+  wk.L_removed = L_removed;
+  wk.L_status = L_status;
+  wk.t_box = t_box;
+  wk.t_area = t_area;
+  wk.s_keptbits = &s_keptbits;
+  wk.s_finish = &s_finish;
+  wk.s_local = s_local;
+  wk.thr = g.thr;
+  wk.max_keep = g.max_keep;
+  wk.nk = 0;
+  wk.fin = 0;
+  wk.stripes_done = 0;
 
   // ---- head: select + sort + walk the first k1 candidates ----
   bool head_ok = false;
@@ -543,21 +347,21 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     if (head_ok) {
       sort_and_redecode(k1, T, 4);
       MXR_STAMP(6);
-      walk_stripes(0, k1);
+      wk.walk(cluster, 0, k1);
     }
   }
   // ---- full list, only if the head did not settle the image ----
   int full_path = 0;
-  if (k > 0 && !fin && (!head_ok || k1 < k)) {
+  if (k > 0 && !wk.fin && (!head_ok || k1 < k)) {
     full_path = 1;
     u64 T = 1ull << 32;
     if (k < n_valid) cluster_select(k, 4, true, &T);
     sort_and_redecode(k, T, 10);
     if (!head_ok) {
-      nk = 0;            // nothing was walked (a run of equal scores is cut by the head boundary)
-      stripes_done = 0;
+      wk.nk = 0;            // nothing was walked (a run of equal scores is cut by the head boundary)
+      wk.stripes_done = 0;
     }
-    walk_stripes(stripes_done, k);
+    wk.walk(cluster, wk.stripes_done, k);
   }
   MXR_STAMP(7);
   if (!head_ok && g.dbg && rank == 0 && tid == 0)
@@ -569,23 +373,21 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       cb->n_valid = n_valid;
       cb->nan_flag = nan_flag;
       cb->n = k;
-      cb->nkept = nk;
+      cb->nkept = wk.nk;
       cb->done = 1;
       cb->pad[0] = 0;
     }
     __syncthreads();
-    coop_write_outputs<double>(g.a, g.o, cb, b, nk, k);
+    coop_write_outputs<double>(g.a, g.o, cb, b, wk.nk, k);
   }
   cluster.sync();  // nobody leaves while its shared memory may still be addressed
   MXR_STAMP(8);
   if (g.dbg && rank == 0 && tid == 0) {
-    g.dbg[(size_t)b * 16 + 9] = (u64)stripes_done;
+    g.dbg[(size_t)b * 16 + 9] = (u64)wk.stripes_done;
     g.dbg[(size_t)b * 16 + 14] = (u64)full_path;
   }
 }
 
-static inline size_t cluster_smem_bytes(int sort_cap) {
-  return (size_t)sort_cap * 8 + (size_t)kCW * kCPitch * 8 + 8 * 8 + 32 * 16 * (sizeof(double4) + sizeof(double)) + 256;
-}
+static inline size_t cluster_smem_bytes(int sort_cap) { return (size_t)sort_cap * 8 + cluster_nms_smem_bytes<double>(); }
 
 }  // namespace mxr

@@ -48,3 +48,32 @@ def nms(dets, thresh, max_keep=0, handle=None):
     _lib.check(lib.mxr_nms_host(h.ptr, _lib.hptr(d), n, 1 if d.dtype == np.float64 else 0, float(thresh),
                                 int(max_keep), _lib.hptr(keep), _lib.hptr(nk)))
     return [int(i) for i in keep[:int(nk[0])]]
+
+
+def nms_batched(dets_list, thresh, max_keep=0, handle=None):
+    """Extension: the per-class loop of rcnn/tester.py:50-56 (``nms(cls_dets, TEST.NMS)`` for every class)
+    as ONE launch.  ``dets_list``: list of (n_c,5) numpy arrays of one dtype (float32 or float64).
+    Returns a list of python lists, element c equal to ``nms(dets_list[c], thresh)``."""
+    lib = _lib.load()
+    h = handle or _lib.default_handle()
+    if len(dets_list) == 0:
+        return []
+    dt = np.float32 if all(np.asarray(d).dtype == np.float32 for d in dets_list) else np.float64
+    arrs = [np.ascontiguousarray(np.asarray(d)[:, :5], dtype=dt).reshape(-1, 5) for d in dets_list]
+    offsets = np.zeros((len(arrs) + 1,), dtype=np.int32)
+    offsets[1:] = np.cumsum([a.shape[0] for a in arrs])
+    total = int(offsets[-1])
+    if total == 0:
+        return [[] for _ in arrs]
+    import torch  # the batched entry point takes device pointers; staging goes through torch here
+    dev = torch.device("cuda", h.device)
+    flat = torch.from_numpy(np.concatenate(arrs, axis=0)).to(dev)
+    keep = torch.empty((total,), dtype=torch.int32, device=dev)
+    nk = torch.zeros((len(arrs), 2), dtype=torch.int32, device=dev)
+    _lib.check(lib.mxr_nms_batched(h.ptr, _lib.current_stream_ptr(flat), flat.data_ptr(),
+                                   offsets.ctypes.data_as(_lib.c_int_p), len(arrs), 1 if dt == np.float64 else 0,
+                                   float(thresh), int(max_keep), keep.data_ptr(), nk.data_ptr()))
+    keep_h, nk_h = keep.cpu().numpy(), nk.cpu().numpy()
+    if (nk_h[:, 1] & 1).any():
+        raise ValueError("nms: NaN in dets")
+    return [[int(i) for i in keep_h[offsets[c]:offsets[c] + nk_h[c, 0]]] for c in range(len(arrs))]

@@ -74,3 +74,29 @@ def test_nms_device_array_and_nan():
     bad[3, 1] = np.nan
     with pytest.raises(ValueError):
         gpu_nms(bad, 0.3)
+
+
+def test_nms_batched_per_class_loop():
+    """rcnn/tester.py:50-56: one nms per class; the batched entry point must equal the loop."""
+    from mxrcnn_b200.helper.processing.nms import nms_batched
+    for dt in (np.float64, np.float32):
+        dets = [synth.class_dets(200 + c, n=n, dtype=dt) for c, n in enumerate([300, 0, 17, 64, 1, 257, 300, 129])]
+        got = nms_batched(dets, 0.3)
+        want = [[int(i) for i in restate.nms(d, 0.3)] if d.shape[0] else [] for d in dets]
+        assert got == want
+    assert nms_batched([], 0.3) == []
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_nms_cluster_and_striped_paths_agree(dtype, monkeypatch):
+    from mxrcnn_b200 import _lib
+    monkeypatch.setenv("MXRCNN_B200_NO_CLUSTER", "1")
+    striped = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_NO_CLUSTER")
+    for n, th in [(300, 0.3), (1025, 0.5), (4000, 0.7), (8192, 0.4)]:
+        dets = synth.class_dets(n + 3, n=n, dtype=dtype, clusters=max(2, n // 50))
+        a = gpu_nms(dets, th)
+        b = gpu_nms(dets, th, handle=striped)
+        assert a == b == [int(i) for i in restate.nms(dets, th)]
+        assert gpu_nms(dets, th, max_keep=50) == a[:50]
+    striped.close()
