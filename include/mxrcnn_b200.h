@@ -159,6 +159,12 @@ int mxr_nms_host(mxr_handle_t h, const void* dets, int n, int dtype, double thre
 int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_t* offsets, int n_problems, int dtype,
                     double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out);
 
+/* ---- helper/processing/nms.py:40-70  nest(dets, thresh) -------------- */
+/* keep_flag[i] = 0 when some other box j has inter(i,j)/area(i) > thresh, else 1; dets (n,5) f32|f64,
+ * arithmetic in that dtype.  The kept list of the reference is the ascending indices with flag 1. */
+int mxr_nest(mxr_handle_t h, void* stream, const void* dets, int n, int dtype, double thresh, int32_t* keep_flag);
+int mxr_nest_host(mxr_handle_t h, const void* dets, int n, int dtype, double thresh, int32_t* keep_flag);
+
 /* ---- A2  helper/processing/bbox_transform.py:35-78  bbox_pred(boxes, box_deltas) -------- */
 /* boxes (n,4) f32|f64 (cast to f64 like :46), deltas (n,c4) f32|f64 (exp evaluated in that dtype),
  * out (n,c4) f64.  n == 0 is a no-op (:43-44).  *_host: all pointers host. */

@@ -77,6 +77,8 @@ SIGNATURES = {
     "mxr_nms_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
     "mxr_nms_batched": (ctypes.c_int, [_VP, _VP, _VP, c_int_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                        ctypes.c_int, _VP, _VP]),
+    "mxr_nest": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, _VP]),
+    "mxr_nest_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, _VP]),
     "mxr_bbox_pred": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, _VP]),
     "mxr_bbox_pred_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, _VP]),
     "mxr_clip_boxes": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,

@@ -77,3 +77,24 @@ def nms_batched(dets_list, thresh, max_keep=0, handle=None):
     if (nk_h[:, 1] & 1).any():
         raise ValueError("nms: NaN in dets")
     return [[int(i) for i in keep_h[offsets[c]:offsets[c] + nk_h[c, 0]]] for c in range(len(arrs))]
+
+
+def nest(dets, thresh=0.90):
+    """Drop every box that lies (almost) inside another one: box i goes when inter(i,j)/area(i) > thresh
+    for some j != i (reference: helper/processing/nms.py:40-70, called from predict.py:75).
+    Returns the python list of kept row indices, ascending."""
+    lib, h = _lib.load(), _lib.default_handle()
+    d = np.asarray(dets)
+    if d.ndim != 2 or d.shape[1] < 4:
+        raise ValueError("dets must be (n, >=4)")
+    if d.dtype != np.float32:
+        d = d.astype(np.float64, copy=False)
+    n = d.shape[0]
+    if n == 0:
+        return []
+    buf = np.zeros((n, 5), dtype=d.dtype)
+    buf[:, :4] = d[:, :4]
+    flags = np.zeros((n,), dtype=np.int32)
+    _lib.check(lib.mxr_nest_host(h.ptr, _lib.hptr(buf), n, 1 if buf.dtype == np.float64 else 0, float(thresh),
+                                 _lib.hptr(flags)))
+    return [int(i) for i in np.where(flags != 0)[0]]

@@ -100,3 +100,14 @@ def test_nms_cluster_and_striped_paths_agree(dtype, monkeypatch):
         assert a == b == [int(i) for i in restate.nms(dets, th)]
         assert gpu_nms(dets, th, max_keep=50) == a[:50]
     striped.close()
+
+
+def test_nest_vs_reference_fixture_and_oracle():
+    from mxrcnn_b200.helper.processing.nms import nest
+    h = golden("helpers")
+    dets = synth.class_dets(40, n=60, dtype=np.float32)
+    assert nest(dets, 0.9) == [int(i) for i in h["nest_keep"]]
+    for n, dt, th in [(1, np.float64, 0.9), (130, np.float64, 0.5), (700, np.float32, 0.9), (300, np.float64, 0.99)]:
+        d = synth.class_dets(90 + n, n=n, dtype=dt, clusters=max(2, n // 30))
+        assert nest(d, th) == restate.nest(d, th)
+    assert nest(np.zeros((0, 5)), 0.9) == []
