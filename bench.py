@@ -450,8 +450,11 @@ def run_gpu_arm(args, rank, world, local_rank):
             per_launch_s = d["us_per_launch"] * 1e-6
             bytes_launch = alg.get(dom, alg["op"]) / max(1.0, 1.0)
             ach = bytes_launch / per_launch_s / 1e9
+            # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel at this
+            # configuration (profiles/r01f_cluster_kernel_ncu.md); not re-measured here (never time under a profiler)
+            traffic = 3554560 if (dom == "proposal_cluster_kernel" and B == 8 and CONFIG == "voc_test") else None
             roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                    "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                     "us_per_launch": d["us_per_launch"], "share_of_step": d["share"]}
         # ALU view of the fused kernel's NMS phase (BASELINE.json: "NMS by SM FP32/ALU-pipe utilisation"):
         # IoU pairs actually evaluated (256-box stripes: in-stripe triangle + kept-so-far x stripe, the latter
