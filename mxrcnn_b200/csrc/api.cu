@@ -3,6 +3,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace mxr {
@@ -49,6 +51,25 @@ int ensure_pinned_ws(Handle* h, size_t bytes) {
   return MXR_OK;
 }
 
+// Kernel attributes and the occupancy figures derived from them, per device, shared by all handles.
+static const int kMaxDevices = 64;
+struct DeviceCache {
+  int smem_attr[8];
+  int coop_grid[4];
+};
+static DeviceCache g_dev_cache[kMaxDevices];
+static std::mutex g_dev_mutex;
+
+int raise_dyn_smem(Handle* h, int slot, const void* func, size_t bytes, int* raised) {
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
+  if (raised) *raised = 0;
+  if ((int)bytes <= h->smem_attr[slot]) return MXR_OK;
+  MXR_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  h->smem_attr[slot] = (int)bytes;
+  if (raised) *raised = 1;
+  return MXR_OK;
+}
+
 }  // namespace mxr
 
 using namespace mxr;
@@ -63,15 +84,20 @@ int mxr_create(int device, mxr_handle_t* out) {
   MXR_REQUIRE(out != nullptr, MXR_ERR_INVALID, "mxr_create: out is NULL");
   int count = 0;
   MXR_CUDA(cudaGetDeviceCount(&count));
-  MXR_REQUIRE(device >= 0 && device < count, MXR_ERR_INVALID, "mxr_create: device %d of %d", device, count);
+  MXR_REQUIRE(device >= 0 && device < count && device < kMaxDevices, MXR_ERR_INVALID, "mxr_create: device %d of %d", device,
+              count);
   MXR_CUDA(cudaSetDevice(device));
   Handle* h = new Handle();
   memset(h, 0, sizeof(*h));
   h->device = device;
+  h->smem_attr = g_dev_cache[device].smem_attr;
+  h->coop_grid = g_dev_cache[device].coop_grid;
   MXR_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   MXR_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
   const char* nc = getenv("MXRCNN_B200_NO_CLUSTER");
   h->no_cluster = (nc && nc[0] == '1') ? 1 : 0;
+  const char* c8 = getenv("MXRCNN_B200_CLUSTER8");
+  h->narrow_clusters = (c8 && c8[0] == '1') ? 1 : 0;
   *out = reinterpret_cast<mxr_handle_t>(h);
   return MXR_OK;
 }

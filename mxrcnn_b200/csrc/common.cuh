@@ -90,10 +90,15 @@ struct Handle {
   ProfRec* prof;
   int prof_cap, prof_used;
   int last_launches;  // kernels launched by the most recent call
-  int smem_attr[8];   // largest dynamic-smem opt-in already set per kernel (0 topk, 1 prep f32, 2 prep f64, 3.. coop)
-  int coop_grid[4];   // co-resident grid size of the cooperative kernels (0: not queried yet)
+  // Both point into the process-wide table of this handle's DEVICE (api.cu): kernel attributes belong to
+  // (kernel, device), not to a handle, so two handles must not cache them separately.
+  int* smem_attr;     // [8] largest dynamic-smem opt-in already set per kernel (1 prep f32, 2 prep f64, 3 coop,
+                      // 4/5 fused proposal, 6/7 cluster NMS); raise it through raise_dyn_smem() only
+  int* coop_grid;     // [4] [0] co-resident grid of the cooperative NMS kernel; [2],[3] how many 16-CTA clusters of
+                      // the fused proposal kernel (4 / 12 keys per thread) fit at once, -1 if none (0: not queried)
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
+  int narrow_clusters;  // MXRCNN_B200_CLUSTER8=1: never use the 16-CTA clusters (tests cover both sizes)
   unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
   int dbg_images;
   cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path
@@ -117,6 +122,10 @@ static inline void prof_end(Handle* h, cudaStream_t s) {
 // Grow-only workspaces.  Growth synchronises the device (never in steady state).
 int ensure_device_ws(Handle* h, size_t bytes);
 int ensure_pinned_ws(Handle* h, size_t bytes);
+// Makes sure kernel `func` may be launched with `bytes` of dynamic shared memory on the handle's device.  The
+// opt-in is cached per (device, slot) for the whole process and only ever raised.  *raised (optional) tells the
+// caller that the limit moved, i.e. that occupancy figures derived from it must be queried again.
+int raise_dyn_smem(Handle* h, int slot, const void* func, size_t bytes, int* raised);
 
 // Bump allocator over the handle's device workspace.
 struct Carver {

@@ -150,10 +150,7 @@ int enqueue_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets, doub
   pa.g_sort_cap = L.n_pow2_max;
   size_t smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 12 : 16;
   const int slot = sizeof(T) == 8 ? 2 : 1;
-  if ((int)smem > h->smem_attr[slot]) {
-    MXR_CUDA(cudaFuncSetAttribute(nms_prepare_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    h->smem_attr[slot] = (int)smem;
-  }
+  MXR_TRY(raise_dyn_smem(h, slot, (const void*)nms_prepare_kernel<T>, smem, nullptr));
   prof_begin(h, s, ST_NMS_PREP);
   nms_prepare_kernel<T><<<L.P, 1024, smem, s>>>(dets, L.offsets, pa, L.n_pow2_max, L.use_smem_sort, L.ctrl);
   prof_end(h, s);
@@ -215,10 +212,7 @@ int enqueue_cluster_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* de
   g.sort_cap = L.n_pow2_max < 1024 ? 1024 : L.n_pow2_max;
   const size_t smem = nms_cluster_smem_bytes<T>(g.sort_cap);
   const int slot = sizeof(T) == 8 ? 7 : 6;
-  if ((int)smem > h->smem_attr[slot]) {
-    MXR_CUDA(cudaFuncSetAttribute(nms_cluster_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    h->smem_attr[slot] = (int)smem;
-  }
+  MXR_TRY(raise_dyn_smem(h, slot, (const void*)nms_cluster_kernel<T>, smem, nullptr));
   const int csize = L.n_max > 1024 ? 8 : (L.n_max > 256 ? 4 : 2);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -433,7 +427,8 @@ int mxr_nms_noalloc(void* stream, const void* dets, int n, int dtype, double thr
   Handle tmp;  // plain host struct for the shared launch helpers: no workspace, profiling off
   memset(&tmp, 0, sizeof(tmp));
   tmp.device = dev;
-  tmp.smem_attr[1] = tmp.smem_attr[2] = 1 << 30;  // <= 24 KiB of dynamic smem here: no opt-in needed
+  int no_opt_in[8] = {0, 1 << 30, 1 << 30, 0, 0, 0, 0, 0};  // <= 24 KiB of dynamic smem here: no opt-in needed
+  tmp.smem_attr = no_opt_in;
   nms_noalloc_reset_kernel<<<4, 256, 0, s>>>(reinterpret_cast<unsigned char*>(L.ctrl), L.zero_bytes, L.offsets, n);
   if (dtype == MXR_DTYPE_F64) {
     MXR_TRY(enqueue_t<double>(&tmp, s, L, reinterpret_cast<const double*>(dets), thresh, max_keep, keep_out, nkeep_out));

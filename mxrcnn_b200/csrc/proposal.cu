@@ -234,19 +234,41 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     const size_t smem_c = cluster_smem_bytes(sort_cap);
     void (*kern)(ClusterArgs) = cluster_items <= 4 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
     const int slot = cluster_items <= 4 ? 4 : 5;
-    if ((int)smem_c > h->smem_attr[slot]) {
-      MXR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
-      h->smem_attr[slot] = (int)smem_c;
+    int raised = 0;
+    MXR_TRY(raise_dyn_smem(h, slot, (const void*)kern, smem_c, &raised));
+    if (raised || h->coop_grid[slot - 2] == 0) {
+      // how many 16-CTA clusters (the opt-in, non-portable size) this device can hold at once
+      int nwide = 0;
+      if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+        cudaLaunchConfig_t q;
+        memset(&q, 0, sizeof(q));
+        q.gridDim = dim3(kClusterSizeMax);
+        q.blockDim = dim3(1024);
+        q.dynamicSmemBytes = smem_c;
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = kClusterSizeMax;
+        qa[0].val.clusterDim.y = 1;
+        qa[0].val.clusterDim.z = 1;
+        q.attrs = qa;
+        q.numAttrs = 1;
+        if (cudaOccupancyMaxActiveClusters(&nwide, kern, &q) != cudaSuccess) nwide = 0;
+      }
+      (void)cudaGetLastError();
+      h->coop_grid[slot - 2] = nwide > 0 ? nwide : -1;
     }
+    // A few images: give each one a 16-CTA cluster (shorter decode/select/NMS phases) as long as all of them
+    // are resident together; otherwise the portable 8-CTA clusters, of which twice as many fit.
+    const int csize = (h->coop_grid[slot - 2] >= L.B && !h->narrow_clusters) ? kClusterSizeMax : kClusterSize;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3(L.B * kClusterSize);
+    cfg.gridDim = dim3(L.B * csize);
     cfg.blockDim = dim3(1024);
     cfg.dynamicSmemBytes = smem_c;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kClusterSize;
+    attr[0].val.clusterDim.x = csize;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -265,12 +287,11 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   if (ca.tier2_at != -1) tier2_smem = L.use_smem_sort ? (size_t)L.n_pow2_max * 8 : 32 * 256 * sizeof(u32);
   const size_t smem2 = coop_smem_bytes(sizeof(double4), sizeof(double), tier2_smem);
   t2.tc.smem_pairs = L.use_smem_sort ? (int)(smem2 / 8) : 0;
-  if (h->coop_grid[0] == 0 || (int)smem2 > h->smem_attr[3]) {
-    MXR_CUDA(cudaFuncSetAttribute(nms_coop_kernel<double, ProposalTier2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem2));
+  int raised2 = 0;
+  MXR_TRY(raise_dyn_smem(h, 3, (const void*)nms_coop_kernel<double, ProposalTier2>, smem2, &raised2));
+  if (h->coop_grid[0] == 0 || raised2) {
     MXR_CUDA(cudaFuncSetAttribute(nms_coop_kernel<double, ProposalTier2>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                   cudaSharedmemCarveoutMaxShared));
-    h->smem_attr[3] = (int)smem2;
     int per_sm = 0, sms = 0;
     MXR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_coop_kernel<double, ProposalTier2>, 1024, smem2));
     MXR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));

@@ -24,7 +24,8 @@
 
 namespace mxr {
 
-static const int kClusterSize = 8;
+static const int kClusterSize = 8;      // portable cluster size: the default
+static const int kClusterSizeMax = 16;  // opt-in size, used when every image's cluster can be resident at once
 static const int kClusterSortMax = 16384;  // largest list the leader sorts in shared memory (128 KiB)
 
 struct ClusterArgs {
@@ -62,8 +63,8 @@ __device__ __forceinline__ void remote_or64(u64* p, u64 v) {
   if (hi) atomicOr(q + 1, hi);
 }
 
-// grid B * kClusterSize CTAs, cluster (kClusterSize,1,1), block 1024.
-// ITEMS: keys per thread; the image's A*hc*wc anchors must fit kClusterSize*ITEMS*1024.
+// grid B * csize CTAs, cluster (csize,1,1) with csize = 8 or 16, block 1024.
+// ITEMS: keys per thread; the image's A*hc*wc anchors must fit csize*ITEMS*1024.
 template <int ITEMS>
 __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g) {
   namespace cgx = cooperative_groups;
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   __shared__ u32 s_hist[256];
   __shared__ u32 s_ghist[12][256];  // leader: cluster-wide digit histograms: head select 0..3, full select 4..10
   __shared__ int s_cnt[4];          // leader: n_valid, nan
-  __shared__ int s_sel[kClusterSize];  // leader: selected count of each CTA
+  __shared__ int s_sel[kClusterSizeMax];  // leader: selected count of each CTA
   __shared__ int s_status[2];       // leader: kept so far, quota reached
   __shared__ u32 s_st[4];
   __shared__ int s_local[4];
@@ -79,7 +80,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   __shared__ int s_finish;
   cgx::cluster_group cluster = cgx::this_cluster();
   const int rank = (int)cluster.block_rank();
-  const int b = blockIdx.x / kClusterSize;
+  const int csize = (int)cluster.num_blocks();
+  const int b = blockIdx.x / csize;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const ProposalGeom& pg = g.pg;
   const DecodeGeom& dg = pg.g;
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   const float* fg = g.cls_prob + (size_t)b * pg.cls_img_stride + pg.cls_fg_offset;
   const float* deltas = g.bbox_pred + (size_t)b * 4 * dg.A * hw;
   const float im_h = __ldg(g.im_info + b * 3), im_w = __ldg(g.im_info + b * 3 + 1), im_s = __ldg(g.im_info + b * 3 + 2);
-  const int chunk = (pg.n_crop + kClusterSize - 1) / kClusterSize;
+  const int chunk = (pg.n_crop + csize - 1) / csize;
   const int q_begin = rank * chunk;
   const int q_end = min(q_begin + chunk, pg.n_crop);
   u32 rk[ITEMS];
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       nnan += __popc(__ballot_sync(0xffffffffu, nan));
     }
     if (pg.cropped) {  // proposal.py:58-62 checks the whole arrays, cropped or not
-      const int fchunk = (pg.n_full + kClusterSize - 1) / kClusterSize;
+      const int fchunk = (pg.n_full + csize - 1) / csize;
       for (int q = rank * fchunk + tid; q < min((rank + 1) * fchunk, pg.n_full); q += 1024) {
         const float v0 = __ldg(fg + q), v1 = __ldg(deltas + q), v2 = __ldg(deltas + q + pg.n_full);
         const float v3 = __ldg(deltas + q + 2 * (size_t)pg.n_full), v4 = __ldg(deltas + q + 3 * (size_t)pg.n_full);
@@ -298,7 +300,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     }
     cluster.sync();
     MXR_STAMP(stamp + 1);
-    const int per = (k_sel + kClusterSize - 1) / kClusterSize;
+    const int per = (k_sel + csize - 1) / csize;
     for (int i = rank * per + tid; i < min((rank + 1) * per, k_sel); i += blockDim.x) {
       const int p = (int)(~(u32)L_sort[i]);
       const int a = p % dg.A, r = p / dg.A;

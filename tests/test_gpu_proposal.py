@@ -171,3 +171,37 @@ def test_fused_cluster_path_equals_multi_kernel_path(cfgname, seed, monkeypatch)
     for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
         assert np.array_equal(fused[k], multi[k]), k
     h.close()
+
+
+@pytest.mark.parametrize("cfgname,seed", [("tiny", 61), ("voc_test", 62), ("voc_train", 63), ("wider", 65)])
+def test_cluster_sizes_agree(cfgname, seed, monkeypatch):
+    """A call with few images runs on 16-CTA clusters, larger batches (or MXRCNN_B200_CLUSTER8=1) on 8-CTA
+    ones: same kernel, same results bit for bit."""
+    from mxrcnn_b200 import _lib
+    cfg = synth.CONFIGS[cfgname]
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    wide = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
+    monkeypatch.setenv("MXRCNN_B200_CLUSTER8", "1")
+    h = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_CLUSTER8")
+    narrow = run(cls, box, info, cfg, rng=np.random.RandomState(seed), handle=h)
+    for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
+        assert np.array_equal(wide[k], narrow[k]), k
+    h.close()
+
+
+def test_two_handles_share_kernel_attributes():
+    """The dynamic shared-memory opt-in belongs to (kernel, device): a second handle that needs less must
+    not lower it under the first one (regression: 'invalid argument' at launch)."""
+    from mxrcnn_b200 import _lib
+    big, small = synth.CONFIGS["voc_test"], synth.CONFIGS["tiny"]
+    a, b = _lib.Handle(0), _lib.Handle(0)
+    ins_big = synth.proposal_inputs(71, H=big["H"], W=big["W"], A=9, im_info=big["im_info"])
+    ins_small = synth.proposal_inputs(72, H=small["H"], W=small["W"], A=9, im_info=small["im_info"])
+    first = run(*ins_big, big, handle=a, rng=np.random.RandomState(1))
+    run(*ins_small, small, handle=b, rng=np.random.RandomState(1))
+    again = run(*ins_big, big, handle=a, rng=np.random.RandomState(1))
+    assert np.array_equal(first["rois"], again["rois"]) and np.array_equal(first["keep"], again["keep"])
+    a.close()
+    b.close()
