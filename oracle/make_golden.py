@@ -216,13 +216,115 @@ def golden_proposal_target(R):
         print("sample_rois", seed)
 
 
+class _FakeSymbol(object):
+    """What rcnn/detector.py:38-58 asks of an mx Symbol: shapes, names, and an executor whose outputs are the
+    network outputs we supply (the network itself is outside the path)."""
+
+    def __init__(self, rois5, scores, deltas, end2end):
+        self._names = ["rpn_rois_output" if end2end else "rois_output", "cls_prob_reshape_output",
+                       "bbox_pred_reshape_output"]
+        self._outs = [ref_shim.NDArrayStub(rois5), ref_shim.NDArrayStub(scores[None]), ref_shim.NDArrayStub(deltas[None])]
+
+    def list_arguments(self):
+        return ["data", "im_info", "cls_prob_label"]
+
+    def infer_shape(self, **kw):
+        return [kw["data"], kw["im_info"], (1,)], [o.shape for o in self._outs], []
+
+    def list_outputs(self):
+        return self._names
+
+    def bind(self, ctx, args, args_grad=None, grad_req="null", aux_states=None):
+        sym = self
+
+        class _Exec(object):
+            outputs = sym._outs
+
+            def forward(self, is_train=False):
+                pass
+        return _Exec()
+
+
+class _Batch(object):
+    def __init__(self, data):
+        self.data = data
+
+
+class _TestData(list):
+    shuffle = False
+
+
+class _FakeImdb(object):
+    def __init__(self, n_images, C, cache):
+        self.num_images, self.num_classes = n_images, C
+        self.classes = ["c%d" % j for j in range(C)]
+        self.cache_path, self.name = cache, "synthetic"
+        self.image_set_index = list(range(n_images))
+        self.all_boxes = None
+
+    def evaluate_detections(self, all_boxes):
+        self.all_boxes = all_boxes
+
+
+def run_reference_box_head(R, cases, nms_thresh=0.3):
+    """The reference's own Detector.im_detect (rcnn/detector.py:17-81) + pred_eval (rcnn/tester.py:10-84) over a
+    list of (rois, deltas, scores, im_shape, scale); returns all_boxes[j][i] as pred_eval hands it to the imdb."""
+    import tempfile
+    T = R.config.TEST
+    saved = (T.HAS_RPN, T.NMS, R.config.END2END)
+    T.HAS_RPN, T.NMS = True, nms_thresh
+    try:
+        C = cases[0][2].shape[1]
+        batches, syms = _TestData(), []
+        for rois, deltas, scores, (im_h, im_w), scale in cases:
+            rois5 = np.hstack((np.zeros((rois.shape[0], 1), np.float32), rois))
+            syms.append(_FakeSymbol(rois5, scores, deltas, R.config.END2END))
+            batches.append(_Batch({"data": np.zeros((1, 3, im_h, im_w), np.float32),
+                                   "im_info": np.array([[im_h, im_w, scale]], dtype=np.float32)}))
+
+        class _Det(R.Detector):  # one fake symbol per image, everything else is the reference's Detector
+            def im_detect(self, im_array, im_info=None, roi_array=None):
+                self.symbol = syms[self.calls]
+                self.calls += 1
+                return R.Detector.im_detect(self, im_array, im_info=im_info, roi_array=roi_array)
+        det = _Det(None, ctx="cpu", arg_params={}, aux_params={})
+        det.calls = 0
+        with tempfile.TemporaryDirectory() as tmp:
+            imdb = _FakeImdb(len(cases), C, tmp)
+            R.pred_eval(det, batches, imdb, vis=False)
+        return imdb.all_boxes
+    finally:
+        T.HAS_RPN, T.NMS, R.config.END2END = saved
+
+
+def golden_box_head(R):
+    # (tag, seed, kwargs of synth.box_head_inputs, nms threshold)
+    specs = [("voc_s0", 0, {}, 0.3), ("voc_s1", 1, {}, 0.3), ("dense_s2", 2, dict(G=2, peaked=0.9), 0.3),
+             ("few_s3", 3, dict(R=40, G=1, peaked=0.1), 0.3), ("big_s4", 4, dict(R=1500, G=12, peaked=0.5), 0.5),
+             ("wider_s5", 5, dict(R=2000, C=2, G=40, peaked=0.7, im_h=1200, im_w=1600, scale=1.0), 0.3)]
+    for tag, seed, kw, thr in specs:
+        case = synth.box_head_inputs(seed, **kw)
+        all_boxes = run_reference_box_head(R, [case], nms_thresh=thr)
+        C = case[2].shape[1]
+        dets = [np.zeros((0, 5))] + [np.asarray(all_boxes[j][0], dtype=np.float64).reshape(-1, 5) for j in range(1, C)]
+        mine, rows = restate.box_head(*case, thresh=0.05, nms_thresh=thr, max_per_image=100)
+        for j in range(C):
+            assert np.array_equal(dets[j], mine[j]), (tag, j)
+        offsets = np.cumsum([0] + [len(d) for d in dets]).astype(np.int32)
+        np.savez_compressed(os.path.join(OUT, "box_head_%s.npz" % tag), seed=seed, kw=np.array(repr(kw)), nms_thresh=thr,
+                            dets=np.concatenate(dets), rows=np.concatenate(rows), offsets=offsets, **meta())
+        print("box_head", tag, "dets", int(offsets[-1]), "of", int((case[2][:, 1:] > 0.05).sum()), "above threshold")
+
+
+GROUPS = {"helpers": golden_helpers, "proposal": golden_proposal, "anchor_target": golden_anchor_target,
+          "proposal_target": golden_proposal_target, "box_head": golden_box_head}
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     R = ref_shim.ref()
-    golden_helpers(R)
-    golden_proposal(R)
-    golden_anchor_target(R)
-    golden_proposal_target(R)
+    for name in (sys.argv[1:] or list(GROUPS)):  # python -m oracle.make_golden [group ...]
+        GROUPS[name](R)
 
 
 if __name__ == "__main__":

@@ -153,6 +153,13 @@ def _install_stubs():
 
         op.CustomOp, op.CustomOpProp, op.register, op._registry = CustomOp, CustomOpProp, register, _registry
         mx.operator = op
+        # what rcnn/detector.py touches: mx.cpu(), mx.nd.array / mx.nd.zeros (float32 like MXNet's default dtype)
+        nd = types.ModuleType("mxnet.ndarray")
+        nd.array = lambda a, ctx=None: NDArrayStub(np.asarray(a, dtype=np.float32))
+        nd.zeros = lambda shape, ctx=None: NDArrayStub(np.zeros(shape, dtype=np.float32))
+        mx.nd = nd
+        mx.cpu = lambda *a: "cpu"
+        sys.modules["mxnet.ndarray"] = nd
         sys.modules["mxnet"] = mx
         sys.modules["mxnet.operator"] = op
 
@@ -172,6 +179,9 @@ def install():
     if not hasattr(builtins, "xrange"):
         builtins.xrange = range
     _install_stubs()
+    if "cPickle" not in sys.modules:  # rcnn/tester.py:4 (py2 module name)
+        import pickle
+        sys.modules["cPickle"] = pickle
     sys.meta_path.insert(0, _RefFinder())
     _installed = True
     return True
@@ -219,4 +229,6 @@ def ref():
     ns._sample_rois = pt._sample_rois
     mb = importlib.import_module("rcnn.minibatch")
     ns.assign_anchor, ns.sample_rois = mb.assign_anchor, mb.sample_rois
+    ns.Detector = importlib.import_module("rcnn.detector").Detector
+    ns.pred_eval = importlib.import_module("rcnn.tester").pred_eval
     return ns

@@ -536,3 +536,37 @@ def sample_rois(roidb, fg_rois_per_image, rois_per_image, num_classes, cfg=None,
     if record is not None:
         record.update(keep_indexes=keep, fg_this=int(fg_this))
     return rois, labels, bt, bw, overlaps
+
+
+# ----------------------------------------------------------------------------------------
+# N1  test-time box head: rcnn/detector.py:73-79 + the class loop of rcnn/tester.py:50-65
+# ----------------------------------------------------------------------------------------
+def box_head(rois, bbox_deltas, scores, im_shape, scale, thresh=0.05, nms_thresh=0.3, max_per_image=100, tie="stable"):
+    """Detections of one image.  ``rois`` (R,4) f32 (batch column already dropped, detector.py:68),
+    ``bbox_deltas`` (R,4C) f32, ``scores`` (R,C) f32, ``im_shape`` = (h, w) of the network input,
+    ``scale`` = im_info[0, 2] (np.float32) or a python float.
+
+    Returns ``(dets, rows)``: per class j (index 0 = background = empty) the (n_j,5) float64 array
+    ``all_boxes[j][i]`` of tester.py:56,64 and the roi row each detection came from.
+    """
+    pred = clip_boxes(bbox_pred(rois, bbox_deltas), im_shape)  # detector.py:73-74
+    C = scores.shape[1]
+    dets = [np.zeros((0, 5))]
+    rows = [np.zeros((0,), dtype=np.int64)]
+    for j in range(1, C):  # tester.py:50-56
+        idx = np.where(scores[:, j] > thresh)[0]  # f32 array vs python float: compared in float32
+        cls_scores = scores[idx, j]
+        cls_boxes = pred[idx, j * 4:(j + 1) * 4] / scale  # f64 / (f32 scalar | python float) -> f64
+        cls_dets = np.hstack((cls_boxes, cls_scores[:, np.newaxis]))
+        keep = np.asarray(nms(cls_dets, nms_thresh, tie=tie), dtype=np.int64)
+        dets.append(cls_dets[keep, :])
+        rows.append(idx[keep])
+    if max_per_image > 0:  # tester.py:58-65
+        image_scores = np.hstack([dets[j][:, -1] for j in range(1, C)])
+        if len(image_scores) > max_per_image:
+            image_thresh = np.sort(image_scores)[-max_per_image]
+            for j in range(1, C):
+                k = np.where(dets[j][:, -1] >= image_thresh)[0]
+                dets[j] = dets[j][k, :]
+                rows[j] = rows[j][k]
+    return dets, rows

@@ -126,3 +126,27 @@ def roidb_entry(seed, R=2000, num_classes=21):
     tg[:, 0] = np.where(ov >= 0.5, cls, 0)
     tg[:, 1:] = rs.normal(0, 0.5, size=(R, 4)).astype(np.float32) * (tg[:, :1] > 0)
     return {"max_classes": cls, "max_overlaps": ov, "boxes": rois.astype(np.uint16), "bbox_targets": tg}
+
+
+def box_head_inputs(seed, R=300, C=21, G=6, im_h=600, im_w=1000, scale=1.6, peaked=0.35):
+    """Inputs of the test-time box head (detector.py:60-74): ``rois`` (R,4) f32 jittered around G objects,
+    ``deltas`` (R,4C) f32 ~ N(0,0.1)/N(0,0.2), ``scores`` (R,C) f32 softmax rows: a fraction ``peaked`` of the rois
+    is confident about its object's class, the rest is mostly background.  Scores are made distinct per class."""
+    rs = np.random.RandomState(seed + 700001)
+    gt = gt_boxes(seed, G=G, im_h=im_h, im_w=im_w, num_classes=C)
+    rois = jittered_rois(seed, gt, R=R, im_h=im_h, im_w=im_w, sigma=25.0)[:, 1:5].astype(np.float32)
+    owner = rs.randint(0, G, R) if G else np.zeros(R, dtype=np.int64)
+    deltas = np.empty((R, 4 * C), dtype=np.float32)
+    deltas[:, 0::4] = rs.normal(0, 0.1, (R, C))
+    deltas[:, 1::4] = rs.normal(0, 0.1, (R, C))
+    deltas[:, 2::4] = rs.normal(0, 0.2, (R, C))
+    deltas[:, 3::4] = rs.normal(0, 0.2, (R, C))
+    logits = rs.normal(0, 1.0, (R, C))
+    logits[:, 0] += 3.0
+    hot = rs.uniform(size=R) < peaked
+    if G:
+        cls = gt[owner, 4].astype(np.int64)
+        logits[hot, cls[hot]] += rs.uniform(3.0, 8.0, int(hot.sum()))
+    e = np.exp(logits - logits.max(axis=1, keepdims=True))
+    scores = (e / e.sum(axis=1, keepdims=True)).astype(np.float32)
+    return rois, deltas, scores, (im_h, im_w), np.float32(scale)

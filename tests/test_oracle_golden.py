@@ -134,3 +134,15 @@ def test_sample_rois_golden(seed):
     out = restate.sample_rois(db, 16, 64, 21, rng=np.random.RandomState(seed))
     for a, k in zip(out, ("rois", "labels", "bbox_targets", "inside", "overlaps")):
         assert np.array_equal(a, g[k]), k
+
+
+@pytest.mark.parametrize("name", golden_names("box_head_"))
+def test_box_head_golden(name):
+    """rcnn/detector.py:73-74 + rcnn/tester.py:50-65 as run by the reference's own Detector / pred_eval."""
+    from tests.util import box_head_case
+    case, thr, dets, rows = box_head_case(golden(name))
+    mine, mrows = restate.box_head(*case, thresh=0.05, nms_thresh=thr, max_per_image=100)
+    assert len(mine) == len(dets) == case[2].shape[1]
+    for j in range(len(dets)):
+        assert mine[j].dtype == np.float64 and np.array_equal(mine[j], dets[j]), j
+        assert np.array_equal(mrows[j], rows[j]), j

@@ -54,3 +54,15 @@ def test_sample_rois_live(R):
     got = restate.sample_rois_e2e(rois, gt, 32, 128, 21, "TRAIN", cfg=cfg, rng=np.random.RandomState(5))
     for a, b in zip(want, got):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("seed,kw", [(30, {}), (31, dict(R=120, G=3, peaked=0.8)), (32, dict(C=2, R=500, G=20))])
+def test_box_head_live(R, seed, kw):
+    """The reference's own Detector.im_detect + pred_eval (driven as in oracle/make_golden.py) on two images."""
+    from oracle.make_golden import run_reference_box_head
+    cases = [synth.box_head_inputs(seed, **kw), synth.box_head_inputs(seed + 100, **kw)]
+    all_boxes = run_reference_box_head(R, cases, nms_thresh=0.3)
+    for i, case in enumerate(cases):
+        mine, _ = restate.box_head(*case, thresh=0.05, nms_thresh=0.3, max_per_image=100)
+        for j in range(1, case[2].shape[1]):
+            assert np.array_equal(np.asarray(all_boxes[j][i]).reshape(-1, 5), mine[j]), (i, j)

@@ -25,3 +25,14 @@ def proposal_case(g):
     pad = pad if pad != (0, 0) else None
     cls, box, info = synth.proposal_inputs(int(g["seed"]), H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"], pad_hw=pad)
     return cls, box, info, cfg, bool(g["train"])
+
+
+def box_head_case(g):
+    """(inputs of synth.box_head_inputs, nms threshold, per-class dets, per-class roi rows) of a box_head_* fixture."""
+    import ast
+    kw = ast.literal_eval(str(g["kw"]))
+    case = synth.box_head_inputs(int(g["seed"]), **kw)
+    off = g["offsets"]
+    dets = [g["dets"][off[j]:off[j + 1]] for j in range(len(off) - 1)]
+    rows = [g["rows"][off[j]:off[j + 1]] for j in range(len(off) - 1)]
+    return case, float(g["nms_thresh"]), dets, rows
