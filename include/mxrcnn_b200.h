@@ -165,6 +165,35 @@ int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_
 int mxr_nest(mxr_handle_t h, void* stream, const void* dets, int n, int dtype, double thresh, int32_t* keep_flag);
 int mxr_nest_host(mxr_handle_t h, const void* dets, int n, int dtype, double thresh, int32_t* keep_flag);
 
+/* ---- test-time box head ------------------------------------------------
+ * rcnn/detector.py:73-74 (pred_boxes = clip_boxes(bbox_pred(rois, bbox_deltas), im_shape)) followed by the
+ * class loop of rcnn/tester.py:50-65: for every foreground class j, rows with scores[:, j] > score_thresh
+ * (compared in float32, as numpy does for a float32 array and a python float), boxes / scale, float64 greedy
+ * NMS (nms.py:4-38) at nms_thresh, and finally the cap: when more than max_per_image detections survive over
+ * all classes, only those with score >= the max_per_image-th largest score stay (ties stay, tester.py:60-65).
+ * One launch for the whole batch. */
+#define MXR_BOX_HEAD_MAX_ROIS 4096
+typedef struct {
+  int32_t n_images;      /* B; the reference handles one image per call */
+  int32_t n_rois;        /* R rows per image, <= MXR_BOX_HEAD_MAX_ROIS */
+  int32_t n_classes;     /* C, background (class 0) included */
+  int32_t max_per_image; /* tester.py:24: 100; <= 0: no cap */
+  double score_thresh;   /* tester.py:22: 0.05 */
+  double nms_thresh;     /* config.TEST.NMS */
+} mxr_box_head_params;
+/* rois dev (B,R,4) f32 (batch column dropped, detector.py:68); bbox_deltas dev (B,R,4C) f32; scores dev (B,R,C) f32;
+ * im dev (B,3) f64: height and width of the network input (im_array.shape[-2:]) and the scale the boxes are
+ * divided by (im_info[0,2], tester.py:39,53).
+ * dets_out dev (B,C,R,5) f64: rows [0, count) of class j are all_boxes[j][i] = [x1,y1,x2,y2,score] in
+ * descending score; rows_out dev (B,C,R) i32: the roi row of each detection; count_out dev (B,C,2) i32:
+ * [detections after the cap, detections after NMS].  Class 0 always has count 0. */
+int mxr_box_head(mxr_handle_t h, void* stream, const mxr_box_head_params* p, const float* rois, const float* bbox_deltas,
+                 const float* scores, const double* im, double* dets_out, int32_t* rows_out, int32_t* count_out);
+/* Same with HOST arrays (copies staged through the workspace); only rows [0, count) of each class list are
+ * guaranteed to be written. */
+int mxr_box_head_host(mxr_handle_t h, const mxr_box_head_params* p, const float* rois, const float* bbox_deltas,
+                      const float* scores, const double* im, double* dets_out, int32_t* rows_out, int32_t* count_out);
+
 /* ---- A2  helper/processing/bbox_transform.py:35-78  bbox_pred(boxes, box_deltas) -------- */
 /* boxes (n,4) f32|f64 (cast to f64 like :46), deltas (n,c4) f32|f64 (exp evaluated in that dtype),
  * out (n,c4) f64.  n == 0 is a no-op (:43-44).  *_host: all pointers host. */

@@ -46,6 +46,11 @@ class ProposalTargetParams(ctypes.Structure):
                 ("means", ctypes.c_double * 4), ("stds", ctypes.c_double * 4), ("inside_weights", ctypes.c_float * 4)]
 
 
+class BoxHeadParams(ctypes.Structure):
+    _fields_ = [("n_images", ctypes.c_int32), ("n_rois", ctypes.c_int32), ("n_classes", ctypes.c_int32),
+                ("max_per_image", ctypes.c_int32), ("score_thresh", ctypes.c_double), ("nms_thresh", ctypes.c_double)]
+
+
 # every symbol include/mxrcnn_b200.h declares: name -> (restype, argtypes)
 _VP = ctypes.c_void_p
 SIGNATURES = {
@@ -79,6 +84,8 @@ SIGNATURES = {
                                        ctypes.c_int, _VP, _VP]),
     "mxr_nest": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, _VP]),
     "mxr_nest_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, _VP]),
+    "mxr_box_head": (ctypes.c_int, [_VP, _VP, ctypes.POINTER(BoxHeadParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "mxr_box_head_host": (ctypes.c_int, [_VP, ctypes.POINTER(BoxHeadParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "mxr_bbox_pred": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, _VP]),
     "mxr_bbox_pred_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, _VP]),
     "mxr_clip_boxes": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmxrcnn_b200.so")
-SOURCES = ["api.cu", "proposal.cu", "nms.cu", "boxes.cu", "targets.cu", "microbench.cu", "nest.cu"]
+SOURCES = ["api.cu", "proposal.cu", "nms.cu", "boxes.cu", "targets.cu", "microbench.cu", "nest.cu", "box_head.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-fmad=false",  # parity: never contract a*b+c (the reference rounds every numpy op)

@@ -69,7 +69,8 @@ enum Stage {
   ST_NMS_COOP = 10,
   ST_CLUSTER = 11,
   ST_NMS_CLUSTER = 12,
-  ST_COUNT = 13
+  ST_BOX_HEAD = 13,
+  ST_COUNT = 14
 };
 
 struct ProfRec {
