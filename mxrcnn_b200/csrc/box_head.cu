@@ -45,16 +45,27 @@ __device__ u32 kth_largest_key(const BoxHeadArgs& g, int b, const int* prefix, i
       if (pass == 0 || ((key ^ pref) >> (shift + 8)) == 0u) atomicAdd(&hist[(key >> shift) & 255u], 1u);
     }
     __syncthreads();
-    if (tid == 0) {
-      u32 cum = 0;
-      for (int d = 255; d >= 0; --d) {
-        const u32 c = hist[d];
-        if (cum + c >= (u32)k_rem) {
-          st[0] = (u32)d;
-          st[1] = (u32)k_rem - cum;
-          break;
+    if (tid < 32) {  // descending scan of the 256 bins: 8 bins per lane, then a shuffle scan over the lanes
+      u32 mine = 0;
+      for (int q = 0; q < 8; ++q) mine += hist[255 - 8 * tid - q];
+      u32 incl = mine;
+      for (int o = 1; o < 32; o <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (tid >= o) incl += v;
+      }
+      const u32 excl = incl - mine;
+      if (excl < (u32)k_rem && (u32)k_rem <= incl) {
+        u32 cum = excl;
+        for (int q = 0; q < 8; ++q) {
+          const int d = 255 - 8 * tid - q;
+          const u32 c = hist[d];
+          if (cum + c >= (u32)k_rem) {
+            st[0] = (u32)d;
+            st[1] = (u32)k_rem - cum;
+            break;
+          }
+          cum += c;
         }
-        cum += c;
       }
     }
     __syncthreads();
@@ -373,21 +384,18 @@ int mxr_box_head_host(mxr_handle_t hh, const mxr_box_head_params* p, const float
   MXR_CUDA(cudaMemcpyAsync(d_im, im, B * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
   MXR_TRY(mxr_box_head(hh, s, p, d_rois, d_deltas, d_scores, d_im, d_dets, d_rows, d_count));
   MXR_CUDA(cudaMemcpyAsync(count_out, d_count, B * C * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-  if (B * C * R * 5 * sizeof(double) <= ((size_t)2 << 20)) {  // small: two copies beat one per class
-    MXR_CUDA(cudaMemcpyAsync(dets_out, d_dets, B * C * R * 5 * sizeof(double), cudaMemcpyDeviceToHost, s));
-    MXR_CUDA(cudaMemcpyAsync(rows_out, d_rows, B * C * R * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaStreamSynchronize(s));
+  // Only the filled head of every class list travels back: one strided copy per array, `most` rows per list
+  // (typically ~10 of R rows: max_per_image detections spread over the classes).
+  size_t most = 0;
+  for (size_t bc = 0; bc < B * C; ++bc) most = (size_t)count_out[bc * 2] > most ? (size_t)count_out[bc * 2] : most;
+  if (most > 0) {
+    MXR_CUDA(cudaMemcpy2DAsync(dets_out, R * 5 * sizeof(double), d_dets, R * 5 * sizeof(double), most * 5 * sizeof(double), B * C,
+                               cudaMemcpyDeviceToHost, s));
+    MXR_CUDA(cudaMemcpy2DAsync(rows_out, R * sizeof(int32_t), d_rows, R * sizeof(int32_t), most * sizeof(int32_t), B * C,
+                               cudaMemcpyDeviceToHost, s));
     MXR_CUDA(cudaStreamSynchronize(s));
-    return MXR_OK;
   }
-  MXR_CUDA(cudaStreamSynchronize(s));
-  // large: only the filled part of each class list travels back (typically ~100 rows of C*R per image)
-  for (size_t bc = 0; bc < B * C; ++bc) {
-    const size_t n = (size_t)count_out[bc * 2];
-    if (n == 0) continue;
-    MXR_CUDA(cudaMemcpyAsync(dets_out + bc * R * 5, d_dets + bc * R * 5, n * 5 * sizeof(double), cudaMemcpyDeviceToHost, s));
-    MXR_CUDA(cudaMemcpyAsync(rows_out + bc * R, d_rows + bc * R, n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-  }
-  MXR_CUDA(cudaStreamSynchronize(s));
   return MXR_OK;
 }
 

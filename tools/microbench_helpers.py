@@ -46,6 +46,26 @@ def main():
     allr = np.vstack((synth.jittered_rois(5, gt, R=2000), np.hstack((np.zeros((8, 1), np.float32), gt[:, :4]))))
     rows.append(("_sample_rois 2008x8", timeit(lambda: _sample_rois(allr, gt, 32, 128, 21, "TRAIN"), n=10),
                  timeit(lambda: restate.sample_rois_e2e(allr, gt, 32, 128, 21, "TRAIN"), n=3, warm=1)))
+    from mxrcnn_b200 import _lib
+    from mxrcnn_b200.rcnn.tester import detections, detections_batch
+    for tag, kw in (("box head 300x21", {}), ("box head 2000x2 (wider)", dict(R=2000, C=2, G=40, peaked=0.7, im_h=1200, im_w=1600, scale=1.0))):
+        r, d, sc, shp, scl = synth.box_head_inputs(7, **kw)
+        rows.append((tag, timeit(lambda: detections(sc, r, d, shp, scl)), timeit(lambda: restate.box_head(r, d, sc, shp, scl), n=3, warm=1)))
+    cases = [synth.box_head_inputs(60 + i) for i in range(8)]
+    r8, d8, s8 = (np.stack([c[k] for c in cases]) for k in range(3))
+    rows.append(("box head 8 x 300x21", timeit(lambda: detections_batch(s8, r8, d8, [(600, 1000)] * 8, [np.float32(1.6)] * 8)),
+                 8 * rows[-2][2]))
+    h = _lib.default_handle()
+    h.profile_enable(True)
+    r, d, sc, shp, scl = synth.box_head_inputs(7, R=2000, C=2, G=40, peaked=0.7, im_h=1200, im_w=1600, scale=1.0)
+    for tag, fn in (("1 image 300x21", lambda: detections(cases[0][2], cases[0][0], cases[0][1], (600, 1000), np.float32(1.6))),
+                    ("8 images 300x21", lambda: detections_batch(s8, r8, d8, [(600, 1000)] * 8, [np.float32(1.6)] * 8)),
+                    ("1 image 2000x2", lambda: detections(sc, r, d, shp, scl))):
+        for _ in range(10):
+            fn()
+        ms, cnt = h.profile_read()["box_head_kernel"]
+        print("box_head_kernel alone, %s: %.1f us" % (tag, ms / cnt * 1e3))
+    h.profile_enable(False)
     print("%-28s %12s %16s" % ("call (host arrays)", "GPU path us", "numpy restate us"))
     for name, a, b in rows:
         print("%-28s %12.1f %16.1f" % (name, a, b))
