@@ -70,3 +70,25 @@ def expand_bbox_regression_targets(bbox_targets_data, num_classes):
         _lib.check(lib.mxr_expand_bbox_targets_host(h.ptr, _lib.hptr(d), k, int(num_classes),
                                                     iw.ctypes.data_as(_lib.c_float_p), _lib.hptr(t), _lib.hptr(w)))
     return t, w
+
+
+def compute_bbox_regression_targets(rois, overlaps, labels):
+    """(k,5) float32 [class, dx, dy, dw, dh] of one image's roidb entry (reference: bbox_regression.py:34-64):
+    every roi with max overlap >= TRAIN.BBOX_REGRESSION_THRESH regresses onto the ground-truth roi (overlap == 1)
+    it overlaps most; IoU + argmax and the transform run on the GPU."""
+    rois = np.asarray(rois).astype(np.float64, copy=False)
+    gt_inds = np.where(overlaps == 1)[0]
+    if len(gt_inds) == 0:
+        print('something wrong : zero ground truth rois')
+    ex_inds = np.where(overlaps >= config.TRAIN.BBOX_REGRESSION_THRESH)[0]
+    targets = np.zeros((rois.shape[0], 5), dtype=np.float32)
+    if len(ex_inds) and len(gt_inds) == 0:
+        raise ValueError("attempt to get argmax of an empty sequence")  # what the reference's argmax raises (:57)
+    if len(ex_inds) == 0:
+        return targets
+    ex_rois = np.ascontiguousarray(rois[ex_inds, :4])
+    gt_assignment = bbox_overlaps_reduced(ex_rois, np.ascontiguousarray(rois[gt_inds, :4]))[0]
+    gt_rois = np.ascontiguousarray(rois[gt_inds[gt_assignment], :4])
+    targets[ex_inds, 0] = labels[ex_inds]
+    targets[ex_inds, 1:] = bbox_transform(ex_rois, gt_rois)
+    return targets

@@ -316,7 +316,63 @@ def golden_box_head(R):
         print("box_head", tag, "dets", int(offsets[-1]), "of", int((case[2][:, 1:] > 0.05).sum()), "above threshold")
 
 
-GROUPS = {"helpers": golden_helpers, "proposal": golden_proposal, "anchor_target": golden_anchor_target,
+def run_reference_roidb(R, gt_roidb, box_list, C, precomputed):
+    """The reference's offline chain on one synthetic dataset: IMDB.create_roidb_from_box_list + merge_roidbs
+    (helper/dataset/imdb.py:32-79), the max_overlaps / max_classes lines of prepare_roidb (helper/processing/roidb.py:27-31;
+    the image-path and cv2.imread lines around them are dataset IO), add_bbox_regression_targets (roidb.py:42-90) on
+    the images that have ground truth, and the report printed by IMDB.evaluate_recall (imdb.py:109-188)."""
+    import contextlib
+    import copy
+    import io
+    imdb = R.IMDB("synthetic")
+    imdb.num_classes, imdb.num_images = C, len(box_list)
+    imdb.classes = ["c%d" % j for j in range(C)]
+    imdb.image_set_index = list(range(len(box_list)))
+    sink = io.StringIO()
+    with contextlib.redirect_stdout(sink):
+        ss = imdb.create_roidb_from_box_list(box_list, gt_roidb)
+        ss_overlaps = [e["gt_overlaps"].toarray() for e in ss]
+        roidb = R.IMDB.merge_roidbs(copy.deepcopy(gt_roidb), ss)
+        for e in roidb:
+            dense = e["gt_overlaps"].toarray()
+            e["max_overlaps"], e["max_classes"] = dense.max(axis=1), dense.argmax(axis=1)
+        with_gt = [e for e in roidb if (e["max_overlaps"] == 1).any()]
+        saved = R.config.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED
+        R.config.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED = precomputed
+        try:
+            means, stds = R.add_bbox_regression_targets(with_gt)
+        finally:
+            R.config.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED = saved
+    report = io.StringIO()
+    with contextlib.redirect_stdout(report):
+        imdb.evaluate_recall(roidb)
+        imdb.evaluate_recall(roidb, area="medium", limit=100)
+    return ss_overlaps, roidb, with_gt, means, stds, report.getvalue()
+
+
+def golden_roidb(R):
+    for seed, pre, kw in [(0, False, {}), (1, True, dict(n_images=3, R=120, C=5, max_gt=3))]:
+        C = kw.get("C", 21)
+        gt_roidb, box_list = synth.gt_roidb_and_box_list(seed, **kw)
+        ss_overlaps, roidb, with_gt, means, stds, report = run_reference_roidb(R, gt_roidb, box_list, C, pre)
+        cfg = restate.default_config()
+        cfg.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED = pre
+        for i, want in enumerate(ss_overlaps):
+            mine = restate.box_list_overlaps(box_list[i], gt_roidb[i]["boxes"], gt_roidb[i]["gt_classes"], C)
+            assert np.array_equal(mine, want), i
+        mine_db = [dict(boxes=e["boxes"], max_overlaps=e["max_overlaps"], max_classes=e["max_classes"],
+                        gt_overlaps=e["gt_overlaps"]) for e in with_gt]
+        m2, s2 = restate.add_bbox_regression_targets(mine_db, cfg)
+        assert np.array_equal(m2, means) and np.array_equal(s2, stds)
+        for a, b in zip(mine_db, with_gt):
+            assert np.array_equal(a["bbox_targets"], b["bbox_targets"])
+        np.savez_compressed(os.path.join(OUT, "roidb_s%d.npz" % seed), seed=seed, kw=np.array(repr(kw)), precomputed=pre,
+                            ss_overlaps=np.concatenate(ss_overlaps), bbox_targets=np.concatenate([e["bbox_targets"] for e in with_gt]),
+                            means=means, stds=stds, recall_report=np.array(report), **meta())
+        print("roidb", seed, "images", len(roidb), "with gt", len(with_gt), "report lines", report.count("\n"))
+
+
+GROUPS = {"roidb": golden_roidb, "helpers": golden_helpers, "proposal": golden_proposal, "anchor_target": golden_anchor_target,
           "proposal_target": golden_proposal_target, "box_head": golden_box_head}
 
 

@@ -69,6 +69,8 @@ def _rewrite_prints(src):
 def _rewrite(src, relpath):
     src = _rewrite_prints(src)
     src = src.replace("from bbox_transform import", "from helper.processing.bbox_transform import")
+    src = src.replace("from bbox_regression import", "from helper.processing.bbox_regression import")  # roidb.py:10
+    src = src.replace("areas.has_key(area)", "(area in areas)")  # helper/dataset/imdb.py:124 (py2 dict method)
     src = src.replace("config.TRAIN.BATCH_SIZE / self._img_per_batch",
                       "config.TRAIN.BATCH_SIZE // self._img_per_batch")
     src = src.replace("config.TRAIN.BATCH_SIZE / config.TRAIN.BATCH_IMAGES",
@@ -229,6 +231,8 @@ def ref():
     ns._sample_rois = pt._sample_rois
     mb = importlib.import_module("rcnn.minibatch")
     ns.assign_anchor, ns.sample_rois = mb.assign_anchor, mb.sample_rois
+    ns.add_bbox_regression_targets = importlib.import_module("helper.processing.roidb").add_bbox_regression_targets
+    ns.IMDB = importlib.import_module("helper.dataset.imdb").IMDB
     ns.Detector = importlib.import_module("rcnn.detector").Detector
     ns.pred_eval = importlib.import_module("rcnn.tester").pred_eval
     return ns

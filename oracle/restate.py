@@ -35,13 +35,15 @@ def default_config():
     """Values of rcnn/config.py:4-70 that the hot path reads."""
     c = Cfg()
     c.END2END = 0
+    c.EPS = 1e-14
     c.TRAIN = Cfg(
         BATCH_SIZE=128, BATCH_IMAGES=2, FG_FRACTION=0.25, FG_THRESH=0.5, BG_THRESH_HI=0.5, BG_THRESH_LO=0.1,
         BBOX_INSIDE_WEIGHTS=np.array([1.0, 1.0, 1.0, 1.0]),
         RPN_BATCH_SIZE=256, RPN_FG_FRACTION=0.5, RPN_POSITIVE_OVERLAP=0.7, RPN_NEGATIVE_OVERLAP=0.3,
         RPN_CLOBBER_POSITIVES=False, RPN_BBOX_INSIDE_WEIGHTS=(1.0, 1.0, 1.0, 1.0), RPN_POSITIVE_WEIGHT=-1.0,
         RPN_NMS_THRESH=0.7, RPN_PRE_NMS_TOP_N=12000, RPN_POST_NMS_TOP_N=6000, RPN_MIN_SIZE=16,
-        BBOX_NORMALIZATION_PRECOMPUTED=False, BBOX_MEANS=(0.0, 0.0, 0.0, 0.0), BBOX_STDS=(0.1, 0.1, 0.2, 0.2))
+        BBOX_NORMALIZATION_PRECOMPUTED=False, BBOX_MEANS=(0.0, 0.0, 0.0, 0.0), BBOX_STDS=(0.1, 0.1, 0.2, 0.2),
+        BBOX_REGRESSION_THRESH=0.5)
     c.TEST = Cfg(NMS=0.3, RPN_NMS_THRESH=0.7, RPN_PRE_NMS_TOP_N=6000, RPN_POST_NMS_TOP_N=300, RPN_MIN_SIZE=16)
     return c
 
@@ -570,3 +572,84 @@ def box_head(rois, bbox_deltas, scores, im_shape, scale, thresh=0.05, nms_thresh
                 dets[j] = dets[j][k, :]
                 rows[j] = rows[j][k]
     return dets, rows
+
+
+# ----------------------------------------------------------------------------------------
+# N3  offline roidb users of bbox_overlaps
+# ----------------------------------------------------------------------------------------
+def compute_bbox_regression_targets(rois, overlaps, labels, cfg=None):
+    """helper/processing/bbox_regression.py:34-64 -> (k,5) float32 [class, dx, dy, dw, dh]."""
+    cfg = cfg or default_config()
+    rois = rois.astype(np.float64, copy=False)  # :43
+    gt_inds = np.where(overlaps == 1)[0]  # :46
+    ex_inds = np.where(overlaps >= cfg.TRAIN.BBOX_REGRESSION_THRESH)[0]  # :50
+    ex_gt = bbox_overlaps(rois[ex_inds, :], rois[gt_inds, :])  # :53
+    gt_assignment = ex_gt.argmax(axis=1)  # :57
+    gt_rois = rois[gt_inds[gt_assignment], :]
+    ex_rois = rois[ex_inds, :]
+    targets = np.zeros((rois.shape[0], 5), dtype=np.float32)
+    targets[ex_inds, 0] = labels[ex_inds]
+    targets[ex_inds, 1:] = bbox_transform(ex_rois, gt_rois)  # f64 -> f32 on assignment
+    return targets
+
+
+def add_bbox_regression_targets(roidb, cfg=None):
+    """helper/processing/roidb.py:42-90: per-image targets, then per-class mean/std normalisation (in place)."""
+    cfg = cfg or default_config()
+    num_images = len(roidb)
+    num_classes = roidb[0]["gt_overlaps"].shape[1]
+    for r in roidb:
+        r["bbox_targets"] = compute_bbox_regression_targets(r["boxes"], r["max_overlaps"], r["max_classes"], cfg)
+    if cfg.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED:  # :58-61
+        means = np.tile(np.array(cfg.TRAIN.BBOX_MEANS), (num_classes, 1))
+        stds = np.tile(np.array(cfg.TRAIN.BBOX_STDS), (num_classes, 1))
+    else:  # :62-79
+        class_counts = np.zeros((num_classes, 1)) + cfg.EPS
+        sums = np.zeros((num_classes, 4))
+        squared_sums = np.zeros((num_classes, 4))
+        for im_i in range(num_images):
+            t = roidb[im_i]["bbox_targets"]
+            for cls in range(1, num_classes):
+                idx = np.where(t[:, 0] == cls)[0]
+                if idx.size > 0:
+                    class_counts[cls] += idx.size
+                    sums[cls, :] += t[idx, 1:].sum(axis=0)
+                    squared_sums[cls, :] += (t[idx, 1:] ** 2).sum(axis=0)
+        means = sums / class_counts
+        stds = np.sqrt(squared_sums / class_counts - means ** 2)
+    for im_i in range(num_images):  # :82-88
+        t = roidb[im_i]["bbox_targets"]
+        for cls in range(1, num_classes):
+            idx = np.where(t[:, 0] == cls)[0]
+            roidb[im_i]["bbox_targets"][idx, 1:] -= means[cls, :]
+            roidb[im_i]["bbox_targets"][idx, 1:] /= stds[cls, :]
+    return means.ravel(), stds.ravel()
+
+
+def box_list_overlaps(boxes, gt_boxes, gt_classes, num_classes):
+    """The per-image body of IMDB.create_roidb_from_box_list (helper/dataset/imdb.py:43-55): dense (n, C) float32
+    with, per box, its best IoU in the column of that gt's class (the reference then wraps it in a csr_matrix)."""
+    overlaps = np.zeros((boxes.shape[0], num_classes), dtype=np.float32)
+    if gt_boxes is not None and gt_boxes.size > 0:
+        gt_overlaps = bbox_overlaps(boxes.astype(np.float64), gt_boxes.astype(np.float64))  # :50
+        argmaxes = gt_overlaps.argmax(axis=1)
+        maxes = gt_overlaps.max(axis=1)
+        idx = np.where(maxes > 0)[0]
+        overlaps[idx, gt_classes[argmaxes[idx]]] = maxes[idx]
+    return overlaps
+
+
+def recall_gt_overlaps(boxes, gt_boxes):
+    """Greedy one-to-one matching of helper/dataset/imdb.py:151-172: the IoU with which each gt box is covered,
+    in the order the loop records them."""
+    overlaps = bbox_overlaps(boxes.astype(np.float64), gt_boxes.astype(np.float64))
+    out = np.zeros((gt_boxes.shape[0]))
+    for j in range(gt_boxes.shape[0]):
+        argmax_overlaps = overlaps.argmax(axis=0)
+        max_overlaps = overlaps.max(axis=0)
+        gt_ind = max_overlaps.argmax()
+        box_ind = argmax_overlaps[gt_ind]
+        out[j] = overlaps[box_ind, gt_ind]
+        overlaps[box_ind, :] = -1
+        overlaps[:, gt_ind] = -1
+    return out

@@ -128,6 +128,32 @@ def roidb_entry(seed, R=2000, num_classes=21):
     return {"max_classes": cls, "max_overlaps": ov, "boxes": rois.astype(np.uint16), "bbox_targets": tg}
 
 
+def gt_roidb_and_box_list(seed, n_images=4, R=300, C=21, max_gt=6, im_h=375, im_w=500):
+    """What IMDB.create_roidb_from_box_list consumes (helper/dataset/imdb.py:32): a ground-truth roidb in the
+    layout of helper/dataset/pascal_voc.py (uint16 boxes, int32 classes, csr one-hot overlaps) and one (R,4) uint16
+    proposal array per image (jittered ground truth plus boxes far from everything).  Image 1 has no ground truth."""
+    import scipy.sparse
+    gt_roidb, box_list = [], []
+    for i in range(n_images):
+        rs = np.random.RandomState(seed * 1000 + i + 900001)
+        G = 0 if i == 1 else int(rs.randint(1, max_gt + 1))
+        gt = gt_boxes(seed * 1000 + i, G=G, im_h=im_h, im_w=im_w, num_classes=C)
+        ov = np.zeros((G, C), dtype=np.float32)
+        ov[np.arange(G), gt[:, 4].astype(np.int64)] = 1.0
+        gt_roidb.append({"boxes": gt[:, :4].astype(np.uint16), "gt_classes": gt[:, 4].astype(np.int32),
+                         "gt_overlaps": scipy.sparse.csr_matrix(ov), "flipped": False})
+        if G:
+            near = jittered_rois(seed * 1000 + i, gt, R=R - R // 4, im_h=im_h, im_w=im_w, sigma=15.0)[:, 1:5]
+        else:
+            near = np.zeros((0, 4), dtype=np.float32)
+        n_far = R - near.shape[0]
+        x1 = rs.uniform(0, im_w - 40, n_far)
+        y1 = rs.uniform(0, im_h - 40, n_far)
+        far = np.stack([x1, y1, x1 + rs.uniform(8, 39, n_far), y1 + rs.uniform(8, 39, n_far)], axis=1)
+        box_list.append(np.vstack((near, far)).astype(np.uint16))
+    return gt_roidb, box_list
+
+
 def box_head_inputs(seed, R=300, C=21, G=6, im_h=600, im_w=1000, scale=1.6, peaked=0.35):
     """Inputs of the test-time box head (detector.py:60-74): ``rois`` (R,4) f32 jittered around G objects,
     ``deltas`` (R,4C) f32 ~ N(0,0.1)/N(0,0.2), ``scores`` (R,C) f32 softmax rows: a fraction ``peaked`` of the rois

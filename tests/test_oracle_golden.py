@@ -146,3 +146,28 @@ def test_box_head_golden(name):
     for j in range(len(dets)):
         assert mine[j].dtype == np.float64 and np.array_equal(mine[j], dets[j]), j
         assert np.array_equal(mrows[j], rows[j]), j
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_roidb_chain_golden(seed):
+    """IMDB.create_roidb_from_box_list + add_bbox_regression_targets as run by the reference (oracle/make_golden.py)."""
+    import ast
+    import scipy.sparse
+    g = golden("roidb_s%d" % seed)
+    kw = ast.literal_eval(str(g["kw"]))
+    C = kw.get("C", 21)
+    gt_roidb, box_list = synth.gt_roidb_and_box_list(seed, **kw)
+    ss = [restate.box_list_overlaps(box_list[i], gt_roidb[i]["boxes"], gt_roidb[i]["gt_classes"], C) for i in range(len(box_list))]
+    assert np.array_equal(np.concatenate(ss), g["ss_overlaps"])
+    db = []
+    for gt, boxes, ov in zip(gt_roidb, box_list, ss):
+        dense = np.vstack((gt["gt_overlaps"].toarray(), ov))
+        if not (dense.max(axis=1) == 1).any():
+            continue
+        db.append(dict(boxes=np.vstack((gt["boxes"], boxes)), gt_overlaps=scipy.sparse.csr_matrix(dense),
+                       max_overlaps=dense.max(axis=1), max_classes=dense.argmax(axis=1)))
+    cfg = restate.default_config()
+    cfg.TRAIN.BBOX_NORMALIZATION_PRECOMPUTED = bool(g["precomputed"])
+    means, stds = restate.add_bbox_regression_targets(db, cfg)
+    assert np.array_equal(means, g["means"]) and np.array_equal(stds, g["stds"])
+    assert np.array_equal(np.concatenate([e["bbox_targets"] for e in db]), g["bbox_targets"])
