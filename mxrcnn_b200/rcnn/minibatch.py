@@ -62,12 +62,16 @@ def sample_rois(roidb, fg_rois_per_image, rois_per_image, num_classes):
 
 
 def assign_anchor(feat_shape, gt_boxes, im_info, feat_stride=16,
-                  scales=(8, 16, 32), ratios=(0.5, 1, 2), allowed_border=0):
+                  scales=(8, 16, 32), ratios=(0.5, 1, 2), allowed_border=0, out=None):
     """RPN labels / bbox targets / weights for one image (reference: minibatch.py:204-395).
 
     Returns the reference's dict: 'label' (1, A*H*W) float32 in (a,h,w) order, 'bbox_target',
     'bbox_inside_weight', 'bbox_outside_weight' (1, 4A, H, W) float32, plus 'gt_boxes' when
     config.END2END == 1.
+
+    ``out`` (extension, used by mxrcnn_b200/rcnn/loader.py): a dict with those four keys holding contiguous float32
+    DEVICE arrays of those shapes (e.g. one image's slices of the batch tensors); the results are written there on
+    the arrays' current stream and never visit the host.
     """
     lib, h = _lib.load(), _lib.default_handle()
     T = config.TRAIN
@@ -111,6 +115,18 @@ def assign_anchor(feat_shape, gt_boxes, im_info, feat_stride=16,
             negative_weight = float(np.float64(1.0 - T.RPN_POSITIVE_WEIGHT) / np.float64(n_fg_final))
     iw = np.ascontiguousarray(T.RPN_BBOX_INSIDE_WEIGHTS, dtype=np.float32)
     N = A * fh * fw
+    if out is not None:
+        views = [_lib.device_view(out[k], np.float32) for k in ('label', 'bbox_target', 'bbox_inside_weight', 'bbox_outside_weight')]
+        if int(np.prod(views[0].shape)) != N or any(int(np.prod(v.shape)) != 4 * N for v in views[1:]):
+            raise ValueError("assign_anchor: `out` arrays do not have %d / %d elements" % (N, 4 * N))
+        _lib.check(lib.mxr_anchor_target_phase2(
+            h.ptr, _lib.current_stream_ptr(out['label']), fg_ranks.ctypes.data_as(_lib.c_int_p), int(fg_ranks.size),
+            bg_ranks.ctypes.data_as(_lib.c_int_p), int(bg_ranks.size), positive_weight, negative_weight,
+            iw.ctypes.data_as(_lib.c_float_p), views[0].ptr, views[1].ptr, views[2].ptr, views[3].ptr))
+        res = dict(out)
+        if config.END2END == 1:
+            res.update({'gt_boxes': gt_boxes})
+        return res
     label = np.empty((1, N), dtype=np.float32)
     tgt = np.empty((1, 4 * A, fh, fw), dtype=np.float32)
     inw = np.empty((1, 4 * A, fh, fw), dtype=np.float32)

@@ -233,6 +233,7 @@ def ref():
     ns.assign_anchor, ns.sample_rois = mb.assign_anchor, mb.sample_rois
     ns.add_bbox_regression_targets = importlib.import_module("helper.processing.roidb").add_bbox_regression_targets
     ns.IMDB = importlib.import_module("helper.dataset.imdb").IMDB
+    ns.generate_detections = importlib.import_module("rcnn.rpn.generate").generate_detections
     ns.Detector = importlib.import_module("rcnn.detector").Detector
     ns.pred_eval = importlib.import_module("rcnn.tester").pred_eval
     return ns

@@ -66,3 +66,47 @@ def test_box_head_live(R, seed, kw):
         mine, _ = restate.box_head(*case, thresh=0.05, nms_thresh=0.3, max_per_image=100)
         for j in range(1, case[2].shape[1]):
             assert np.array_equal(np.asarray(all_boxes[j][i]).reshape(-1, 5), mine[j]), (i, j)
+
+
+def test_rpn_wire_format_live(R, tmp_path):
+    """rcnn/rpn/generate.py:43-77 run for real (fake detector / iterator / imdb) next to the mirror's writer: the two
+    files hold the same list, and each side reads the other's file."""
+    import pickle
+    from mxrcnn_b200.rcnn.rpn import generate as mine
+    rs = np.random.RandomState(3)
+    rois, infos = [], []
+    for i in range(3):
+        b = synth.jittered_rois(i, synth.gt_boxes(i, G=4), R=50)
+        rois.append(b * np.float32(1.6))
+        infos.append(np.array([[600, 1000, 1.6 if i != 1 else 1.25]], dtype=np.float32))
+
+    class Det(object):
+        calls = 0
+
+        def im_detect(self, im, im_info):
+            self.calls += 1
+            return rois[self.calls - 1], rs.uniform(size=(50, 1)).astype(np.float32)
+
+    class Batch(object):
+        def __init__(self, info):
+            self.data = {"data": np.zeros((1, 3, 4, 4), np.float32), "im_info": info}
+
+    class Data(list):
+        shuffle = False
+
+    class Imdb(object):
+        num_images, name = 3, "synthetic"
+        root_path = str(tmp_path / "ref")
+    (tmp_path / "ref").mkdir()
+    (tmp_path / "mine").mkdir()
+    want = R.generate_detections(Det(), Data(Batch(i) for i in infos), Imdb(), vis=False)
+    got = mine.batch_to_box_list(np.concatenate(rois), np.concatenate(infos), 50)
+    assert len(got) == len(want) == 3
+    for a, b in zip(got, want):
+        assert a.dtype == b.dtype == np.float32 and np.array_equal(a, b)
+    mine.write_rpn_file(str(tmp_path / "mine"), "synthetic", got)
+    theirs = mine.read_rpn_file(str(tmp_path / "ref"), "synthetic")           # mirror reads the reference's file
+    with open(mine.rpn_file_path(str(tmp_path / "mine"), "synthetic"), "rb") as f:  # what pascal_voc.py:199-200 does
+        ours = pickle.load(f)
+    for a, b, c in zip(theirs, ours, want):
+        assert np.array_equal(a, c) and np.array_equal(b, c)
