@@ -56,6 +56,7 @@ static const int kMaxDevices = 64;
 struct DeviceCache {
   int smem_attr[8];
   int coop_grid[4];
+  int cluster_cap[8];
 };
 static DeviceCache g_dev_cache[kMaxDevices];
 static std::mutex g_dev_mutex;
@@ -92,12 +93,18 @@ int mxr_create(int device, mxr_handle_t* out) {
   h->device = device;
   h->smem_attr = g_dev_cache[device].smem_attr;
   h->coop_grid = g_dev_cache[device].coop_grid;
+  h->cluster_cap = g_dev_cache[device].cluster_cap;
   MXR_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   MXR_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
   const char* nc = getenv("MXRCNN_B200_NO_CLUSTER");
   h->no_cluster = (nc && nc[0] == '1') ? 1 : 0;
   const char* c8 = getenv("MXRCNN_B200_CLUSTER8");
-  h->narrow_clusters = (c8 && c8[0] == '1') ? 1 : 0;
+  h->cluster_override = (c8 && c8[0] == '1') ? 8 : 0;
+  const char* cs = getenv("MXRCNN_B200_CLUSTER");
+  if (cs) {
+    const int v = atoi(cs);
+    if (v == 2 || v == 4 || v == 8 || v == 16) h->cluster_override = v;
+  }
   *out = reinterpret_cast<mxr_handle_t>(h);
   return MXR_OK;
 }

@@ -95,11 +95,13 @@ struct Handle {
   // (kernel, device), not to a handle, so two handles must not cache them separately.
   int* smem_attr;     // [8] largest dynamic-smem opt-in already set per kernel (1 prep f32, 2 prep f64, 3 coop,
                       // 4/5 fused proposal, 6/7 cluster NMS); raise it through raise_dyn_smem() only
-  int* coop_grid;     // [4] [0] co-resident grid of the cooperative NMS kernel; [2],[3] how many 16-CTA clusters of
-                      // the fused proposal kernel (4 / 12 keys per thread) fit at once, -1 if none (0: not queried)
+  int* coop_grid;     // [4] [0] co-resident grid of the cooperative NMS kernel (0: not queried)
+  int* cluster_cap;   // [2][4] fused proposal kernel (4 / 12 keys per thread) x cluster size (16, 8, 4, 2): clusters
+                      // resident at once; 0 not queried, -1 none
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
-  int narrow_clusters;  // MXRCNN_B200_CLUSTER8=1: never use the 16-CTA clusters (tests cover both sizes)
+  int cluster_override; // MXRCNN_B200_CLUSTER=2|4|8|16 pins the cluster size of the fused proposal kernel (tests cover
+                        // them all); MXRCNN_B200_CLUSTER8=1 is the older spelling of 8.  0: chosen per call
   unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
   int dbg_images;
   cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path

@@ -232,34 +232,54 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     h->dbg_ptr = L.dbg;
     h->dbg_images = L.B;
     const size_t smem_c = cluster_smem_bytes(sort_cap);
-    void (*kern)(ClusterArgs) = cluster_items <= 4 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
-    const int slot = cluster_items <= 4 ? 4 : 5;
-    int raised = 0;
-    MXR_TRY(raise_dyn_smem(h, slot, (const void*)kern, smem_c, &raised));
-    if (raised || h->coop_grid[slot - 2] == 0) {
-      // how many 16-CTA clusters (the opt-in, non-portable size) this device can hold at once
-      int nwide = 0;
-      if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+    // Cluster size per call.  A wide cluster shortens every phase of one image (measured per wave at 38x63x9:
+    // 47 / 54 / 72 / 98 us for 16 / 8 / 4 / 2 CTAs) but fewer of them are resident at once (6 / ~14 / ~36 / 74 on
+    // a B200), so a small batch wants wide clusters and a large one narrow clusters: pick the size that minimises
+    // waves x relative wave time.  MXRCNN_B200_CLUSTER pins it (tests run every size).
+    static const int kSizes[4] = {16, 8, 4, 2};
+    static const double kWaveCost[4] = {0.88, 1.0, 1.35, 1.85};
+    int csize = 0, items = 0;
+    double best = 0;
+    int pinned = h->cluster_override;  // ignored when the image does not fit 12 keys per thread at that size
+    if (pinned && (L.n_crop + pinned * 1024 - 1) / (pinned * 1024) > 12) pinned = 0;
+    for (int c = 0; c < 4; ++c) {
+      const int cs = kSizes[c];
+      if (pinned && pinned != cs) continue;
+      const int it = (L.n_crop + cs * 1024 - 1) / (cs * 1024);
+      if (it > 12) continue;
+      const int v = it <= 4 ? 0 : 1;  // kernel variant: 4 or 12 keys per thread
+      void (*kq)(ClusterArgs) = v == 0 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
+      MXR_TRY(raise_dyn_smem(h, 4 + v, (const void*)kq, smem_c, nullptr));
+      int& cap = h->cluster_cap[v * 4 + c];
+      if (cap == 0) {  // how many clusters of this size the device holds at once (0: not asked yet, -1: none)
         cudaLaunchConfig_t q;
         memset(&q, 0, sizeof(q));
-        q.gridDim = dim3(kClusterSizeMax);
+        q.gridDim = dim3(cs);
         q.blockDim = dim3(1024);
         q.dynamicSmemBytes = smem_c;
         cudaLaunchAttribute qa[1];
         qa[0].id = cudaLaunchAttributeClusterDimension;
-        qa[0].val.clusterDim.x = kClusterSizeMax;
+        qa[0].val.clusterDim.x = cs;
         qa[0].val.clusterDim.y = 1;
         qa[0].val.clusterDim.z = 1;
         q.attrs = qa;
         q.numAttrs = 1;
-        if (cudaOccupancyMaxActiveClusters(&nwide, kern, &q) != cudaSuccess) nwide = 0;
+        int n = 0;
+        if (cs > 8 && cudaFuncSetAttribute(kq, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) n = -1;
+        if (n == 0 && cudaOccupancyMaxActiveClusters(&n, kq, &q) != cudaSuccess) n = -1;
+        (void)cudaGetLastError();
+        cap = n > 0 ? n : -1;
       }
-      (void)cudaGetLastError();
-      h->coop_grid[slot - 2] = nwide > 0 ? nwide : -1;
+      if (cap <= 0) continue;
+      const double cost = (double)((L.B + cap - 1) / cap) * kWaveCost[c];
+      if (csize == 0 || cost < best) {
+        csize = cs;
+        items = it;
+        best = cost;
+      }
     }
-    // A few images: give each one a 16-CTA cluster (shorter decode/select/NMS phases) as long as all of them
-    // are resident together; otherwise the portable 8-CTA clusters, of which twice as many fit.
-    const int csize = (h->coop_grid[slot - 2] >= L.B && !h->narrow_clusters) ? kClusterSizeMax : kClusterSize;
+    MXR_REQUIRE(csize != 0, MXR_ERR_CUDA, "proposal: no cluster size of the fused kernel fits this device");
+    void (*kern)(ClusterArgs) = items <= 4 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(L.B * csize);

@@ -175,20 +175,39 @@ def test_fused_cluster_path_equals_multi_kernel_path(cfgname, seed, monkeypatch)
 
 @pytest.mark.parametrize("cfgname,seed", [("tiny", 61), ("voc_test", 62), ("voc_train", 63), ("wider", 65)])
 def test_cluster_sizes_agree(cfgname, seed, monkeypatch):
-    """A call with few images runs on 16-CTA clusters, larger batches (or MXRCNN_B200_CLUSTER8=1) on 8-CTA
-    ones: same kernel, same results bit for bit."""
+    """The fused kernel runs on clusters of 16, 8, 4 or 2 CTAs, chosen per call from the batch size
+    (MXRCNN_B200_CLUSTER pins one): same kernel, same results bit for bit."""
     from mxrcnn_b200 import _lib
     cfg = synth.CONFIGS[cfgname]
     A = len(cfg["scales"]) * len(cfg["ratios"])
     cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
-    wide = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
-    monkeypatch.setenv("MXRCNN_B200_CLUSTER8", "1")
-    h = _lib.Handle(0)
-    monkeypatch.delenv("MXRCNN_B200_CLUSTER8")
-    narrow = run(cls, box, info, cfg, rng=np.random.RandomState(seed), handle=h)
-    for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
-        assert np.array_equal(wide[k], narrow[k]), k
-    h.close()
+    auto = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
+    for size in ("2", "4", "8", "16"):
+        monkeypatch.setenv("MXRCNN_B200_CLUSTER", size)
+        h = _lib.Handle(0)
+        monkeypatch.delenv("MXRCNN_B200_CLUSTER")
+        pinned = run(cls, box, info, cfg, rng=np.random.RandomState(seed), handle=h)
+        for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
+            assert np.array_equal(auto[k], pinned[k]), (size, k)
+        h.close()
+
+
+@pytest.mark.parametrize("B", [6, 20, 45, 80])
+def test_batch_size_picks_cluster_size_without_changing_results(B):
+    """6 / 20 / 45 / 80 images per call land on 16- / 4- / 2-CTA clusters (several waves at 80); every image must
+    equal its own single-image result."""
+    cfg = synth.CONFIGS["voc_test"]
+    seeds = [200 + (i % 5) for i in range(B)]
+    cls, box, info = synth.proposal_batch(seeds, cfg)
+    out = run(cls, box, info, cfg, rng=np.random.RandomState(0))
+    ones = {}
+    for i in range(5):
+        ones[200 + i] = run(cls[i:i + 1], box[i:i + 1], info[i:i + 1], cfg, rng=np.random.RandomState(0))
+    post = cfg["post"]
+    for i, s in enumerate(seeds):
+        assert np.array_equal(out["keep"][i], ones[s]["keep"][0]), i
+        assert np.array_equal(out["rois"][i * post:(i + 1) * post, 1:], ones[s]["rois"][:, 1:]), i
+        assert np.array_equal(out["scores"][i * post:(i + 1) * post], ones[s]["scores"]), i
 
 
 def test_two_handles_share_kernel_attributes():
