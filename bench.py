@@ -357,6 +357,22 @@ def run_gpu_arm(args, rank, world, local_rank):
     N = A * cfg["H"] * cfg["W"]
     h2d = B * (4 * N + 16 * N + 12)  # fg half of cls_prob + deltas + im_info (the bg half is never copied)
     d2h = B * post * (20 + 4 + 4 + 4) + B * 8
+    # what the host link gives a plain pinned -> device copy of one step's input bytes (the e2e bound on this box)
+    link_gbs = None
+    if rank == 0:
+        pin = torch.empty(h2d, dtype=torch.uint8).pin_memory()
+        dst = torch.empty(h2d, dtype=torch.uint8, device=dev)
+        with torch.cuda.stream(stream):
+            for _ in range(5):
+                dst.copy_(pin, non_blocking=True)
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record(stream)
+            for _ in range(50):
+                dst.copy_(pin, non_blocking=True)
+            c1.record(stream)
+        stream.synchronize()
+        link_gbs = h2d * 50 / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        del pin, dst
 
     # ---- per-kernel profile (separate pass, CUDA events around every launch on the launching stream) ----
     prof_steps = min(args.steps, 50)
@@ -376,7 +392,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         alu[nm] = gv.value
 
     # ---- saturating batch (not the headline): 256 images in one launch = 132 MB of inputs (> L2),
-    #      14 waves of 8-CTA clusters; shows the throughput asymptote of the same kernels ----
+    #      which the library runs as 4 waves of 2-CTA clusters; shows the throughput asymptote of the same kernel ----
     sat = None
     if rank == 0:
         SB = 256
@@ -487,6 +503,8 @@ def run_gpu_arm(args, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": 1e3 * e2e_s / args.steps,
                     "api": "mxr_proposal_submit_host / mxr_proposal_wait_host, two slots (pinned host buffers)",
+                    "bound": "host link (H2D)", "h2d_gbs": h2d / (e2e_s / args.steps) / 1e9,
+                    "h2d_link_gbs_plain_copy": link_gbs,
                     "one_call_at_a_time": {"value": e2e_sync_value, "ms_per_step": 1e3 * e2e_sync_s / args.steps,
                                            "api": "mxr_proposal_forward_host"}},
             "gpu_launches": launches_per_step * args.steps,

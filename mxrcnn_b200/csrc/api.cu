@@ -56,7 +56,7 @@ static const int kMaxDevices = 64;
 struct DeviceCache {
   int smem_attr[8];
   int coop_grid[4];
-  int cluster_cap[8];
+  int cluster_cap[16];
 };
 static DeviceCache g_dev_cache[kMaxDevices];
 static std::mutex g_dev_mutex;
@@ -103,7 +103,7 @@ int mxr_create(int device, mxr_handle_t* out) {
   const char* cs = getenv("MXRCNN_B200_CLUSTER");
   if (cs) {
     const int v = atoi(cs);
-    if (v == 2 || v == 4 || v == 8 || v == 16) h->cluster_override = v;
+    if (v >= 2 && v <= 16 && v % 2 == 0) h->cluster_override = v;
   }
   *out = reinterpret_cast<mxr_handle_t>(h);
   return MXR_OK;

@@ -96,7 +96,7 @@ struct Handle {
   int* smem_attr;     // [8] largest dynamic-smem opt-in already set per kernel (1 prep f32, 2 prep f64, 3 coop,
                       // 4/5 fused proposal, 6/7 cluster NMS); raise it through raise_dyn_smem() only
   int* coop_grid;     // [4] [0] co-resident grid of the cooperative NMS kernel (0: not queried)
-  int* cluster_cap;   // [2][4] fused proposal kernel (4 / 12 keys per thread) x cluster size (16, 8, 4, 2): clusters
+  int* cluster_cap;   // [2][8] fused proposal kernel (4 / 12 keys per thread) x cluster size (16, 14, ... 2): clusters
                       // resident at once; 0 not queried, -1 none
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one

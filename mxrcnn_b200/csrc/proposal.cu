@@ -233,16 +233,18 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     h->dbg_images = L.B;
     const size_t smem_c = cluster_smem_bytes(sort_cap);
     // Cluster size per call.  A wide cluster shortens every phase of one image (measured per wave at 38x63x9:
-    // 47 / 54 / 72 / 98 us for 16 / 8 / 4 / 2 CTAs) but fewer of them are resident at once (6 / ~14 / ~36 / 74 on
-    // a B200), so a small batch wants wide clusters and a large one narrow clusters: pick the size that minimises
-    // waves x relative wave time.  MXRCNN_B200_CLUSTER pins it (tests run every size).
-    static const int kSizes[4] = {16, 8, 4, 2};
-    static const double kWaveCost[4] = {0.88, 1.0, 1.35, 1.85};
+    // 47 / 50 / 54 / 58 / 72 / 98 us for 16 / 12 / 8 / 6 / 4 / 2 CTAs) but fewer of them are resident at once
+    // (7 / 7 / 14 / 16+ / 36 / 74 on a B200: cudaOccupancyMaxActiveClusters), so a small batch wants wide clusters
+    // and a large one narrow clusters: pick the size that minimises waves x relative wave time.
+    // MXRCNN_B200_CLUSTER pins it (tests run several sizes).
+    static const int kNumSizes = 8;
+    static const int kSizes[kNumSizes] = {16, 14, 12, 10, 8, 6, 4, 2};
+    static const double kWaveCost[kNumSizes] = {0.883, 0.89, 0.925, 0.99, 1.0, 1.075, 1.35, 1.85};
     int csize = 0, items = 0;
     double best = 0;
     int pinned = h->cluster_override;  // ignored when the image does not fit 12 keys per thread at that size
     if (pinned && (L.n_crop + pinned * 1024 - 1) / (pinned * 1024) > 12) pinned = 0;
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < kNumSizes; ++c) {
       const int cs = kSizes[c];
       if (pinned && pinned != cs) continue;
       const int it = (L.n_crop + cs * 1024 - 1) / (cs * 1024);
@@ -250,7 +252,7 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
       const int v = it <= 4 ? 0 : 1;  // kernel variant: 4 or 12 keys per thread
       void (*kq)(ClusterArgs) = v == 0 ? proposal_cluster_kernel<4> : proposal_cluster_kernel<12>;
       MXR_TRY(raise_dyn_smem(h, 4 + v, (const void*)kq, smem_c, nullptr));
-      int& cap = h->cluster_cap[v * 4 + c];
+      int& cap = h->cluster_cap[v * kNumSizes + c];
       if (cap == 0) {  // how many clusters of this size the device holds at once (0: not asked yet, -1: none)
         cudaLaunchConfig_t q;
         memset(&q, 0, sizeof(q));

@@ -175,14 +175,14 @@ def test_fused_cluster_path_equals_multi_kernel_path(cfgname, seed, monkeypatch)
 
 @pytest.mark.parametrize("cfgname,seed", [("tiny", 61), ("voc_test", 62), ("voc_train", 63), ("wider", 65)])
 def test_cluster_sizes_agree(cfgname, seed, monkeypatch):
-    """The fused kernel runs on clusters of 16, 8, 4 or 2 CTAs, chosen per call from the batch size
+    """The fused kernel runs on clusters of 2 ... 16 CTAs (even sizes), chosen per call from the batch size
     (MXRCNN_B200_CLUSTER pins one): same kernel, same results bit for bit."""
     from mxrcnn_b200 import _lib
     cfg = synth.CONFIGS[cfgname]
     A = len(cfg["scales"]) * len(cfg["ratios"])
     cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
     auto = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
-    for size in ("2", "4", "8", "16"):
+    for size in ("2", "4", "6", "8", "12", "16"):
         monkeypatch.setenv("MXRCNN_B200_CLUSTER", size)
         h = _lib.Handle(0)
         monkeypatch.delenv("MXRCNN_B200_CLUSTER")

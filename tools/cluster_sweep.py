@@ -17,9 +17,9 @@ def main():
     cfgname = sys.argv[1] if len(sys.argv) > 1 else "voc_test"
     cfg = synth.CONFIGS[cfgname]
     anchors = generate_anchors(float(cfg["feat_stride"]), list(cfg["ratios"]), np.array(cfg["scales"], dtype=float))
-    batches = (1, 4, 8, 16, 18, 32, 37, 64, 74, 128, 256)
+    batches = tuple(int(b) for b in os.environ.get("SWEEP_BATCHES", "1,4,8,16,18,32,37,64,74,128,256").split(","))
     base = synth.proposal_batch(range(3, 3 + 32), cfg)
-    sizes = ("0", "2", "4", "8", "16")
+    sizes = tuple(os.environ.get("SWEEP_SIZES", "0,2,4,8,16").split(","))
     table = {}
     for cs in sizes:
         os.environ["MXRCNN_B200_CLUSTER"] = cs
