@@ -54,6 +54,66 @@ __device__ __forceinline__ void bitonic_sort_1024_regs(u64* buf, int n_pow2) {
   __syncthreads();
 }
 
+// Same sort with FOUR keys per thread on the first 256 threads (blockDim.x == 1024, all threads call it; the other
+// 768 only wait at the end): strides 1-2 are register compare-exchanges, 4..64 warp shuffles, and only strides
+// >= 128 -- 6 of the 55 stages -- go through shared memory, synchronised by a 256-thread named barrier
+// instead of a block-wide one.
+__device__ __forceinline__ void order_pair(u64& a, u64& b, bool desc) {
+  const bool sw = desc ? (b > a) : (a > b);
+  const u64 x = sw ? b : a, y = sw ? a : b;
+  a = x;
+  b = y;
+}
+__device__ __forceinline__ void bitonic_sort_1024_x4(u64* buf, int n_pow2) {
+  const int t = threadIdx.x;
+  if (t < 256) {
+    u64 v[4];
+    {
+      const ulonglong2 lo = reinterpret_cast<const ulonglong2*>(buf)[2 * t], hi = reinterpret_cast<const ulonglong2*>(buf)[2 * t + 1];
+      v[0] = lo.x;
+      v[1] = lo.y;
+      v[2] = hi.x;
+      v[3] = hi.y;
+    }
+    // size 2: pairs (0,1) descending, (2,3) ascending
+    order_pair(v[0], v[1], true);
+    order_pair(v[2], v[3], false);
+    for (int size = 4; size <= n_pow2; size <<= 1) {
+      const bool desc = ((4 * t) & size) == 0;  // the same for the thread's four elements once size >= 4
+      for (int stride = size >> 1; stride >= 4; stride >>= 1) {
+        const int ts = stride >> 2;  // partner thread = t ^ ts
+        u64 o[4];
+        if (stride >= 128) {
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          reinterpret_cast<ulonglong2*>(buf)[2 * t] = make_ulonglong2(v[0], v[1]);
+          reinterpret_cast<ulonglong2*>(buf)[2 * t + 1] = make_ulonglong2(v[2], v[3]);
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          const ulonglong2 lo = reinterpret_cast<const ulonglong2*>(buf)[2 * (t ^ ts)];
+          const ulonglong2 hi = reinterpret_cast<const ulonglong2*>(buf)[2 * (t ^ ts) + 1];
+          o[0] = lo.x;
+          o[1] = lo.y;
+          o[2] = hi.x;
+          o[3] = hi.y;
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) o[q] = __shfl_xor_sync(0xffffffffu, v[q], ts);
+        }
+        const bool take_max = (((t & ts) == 0) == desc);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) v[q] = (take_max == (o[q] > v[q])) ? o[q] : v[q];
+      }
+      order_pair(v[0], v[2], desc);  // stride 2
+      order_pair(v[1], v[3], desc);
+      order_pair(v[0], v[1], desc);  // stride 1
+      order_pair(v[2], v[3], desc);
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    reinterpret_cast<ulonglong2*>(buf)[2 * t] = make_ulonglong2(v[0], v[1]);
+    reinterpret_cast<ulonglong2*>(buf)[2 * t + 1] = make_ulonglong2(v[2], v[3]);
+  }
+  __syncthreads();
+}
+
 // 16 columns of one row: bit j set when column j is suppressed by the row box (nms.py:25-36).
 template <typename T>
 __device__ __forceinline__ u32 tile_bits16(const typename Ar<T>::Box rb, T rarea, const typename Ar<T>::Box* cols,

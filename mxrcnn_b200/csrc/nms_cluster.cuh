@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(1024, 1) nms_cluster_kernel(NmsClusterArgs<T> 
     }
     __syncthreads();
     if (NmsKey<T>::kPayload) bitonic_sort_desc(sortbuf, sortpl, n_pow2);
-    else if (n_pow2 <= 1024) bitonic_sort_1024_regs(sortbuf, n_pow2);
+    else if (n_pow2 <= 1024) bitonic_sort_1024_x4(sortbuf, n_pow2);
     else bitonic_sort_desc_u64(sortbuf, n_pow2);
   }
   cluster.sync();

@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     cluster.sync();
     MXR_STAMP(stamp);
     if (rank == 0) {
-      if (n_pow2 <= 1024) bitonic_sort_1024_regs(sortbuf, n_pow2);
+      if (n_pow2 <= 1024) bitonic_sort_1024_x4(sortbuf, n_pow2);
       else bitonic_sort_desc_u64(sortbuf, n_pow2);
     }
     cluster.sync();
