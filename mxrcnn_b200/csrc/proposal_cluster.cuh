@@ -63,6 +63,15 @@ __device__ __forceinline__ void remote_or64(u64* p, u64 v) {
   if (hi) atomicOr(q + 1, hi);
 }
 
+// Head selection bins: bin(s) = clamp(int(s * kHeadBins), 0, kHeadBins - 1) is monotone in the score, so "bin >= t" is
+// exactly "score >= t / kHeadBins" -- a cut between two distinct scores, never inside a run of equal ones.
+static const int kHeadBins = 1024;
+__device__ __forceinline__ int head_bin_of_key(u32 key) {
+  const u32 bits = (key & 0x80000000u) ? (key & 0x7fffffffu) : ~key;  // inverse of score_key32
+  const int v = (int)(__uint_as_float(bits) * (float)kHeadBins);        // saturating conversion
+  return v < 0 ? 0 : (v > kHeadBins - 1 ? kHeadBins - 1 : v);
+}
+
 // grid B * csize CTAs, cluster (csize,1,1) with csize = 8 or 16, block 1024.
 // ITEMS: keys per thread; the image's A*hc*wc anchors must fit csize*ITEMS*1024.
 template <int ITEMS>
@@ -70,6 +79,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   namespace cgx = cooperative_groups;
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ u32 s_hist[256];
+  __shared__ u32 s_bins[kHeadBins];      // this CTA's counts of its valid scores per linear score bin (head selection)
+  __shared__ u32 s_pack[kHeadBins / 2];  // the same as pairs of 16-bit counts: what the other CTAs read
   __shared__ u32 s_ghist[12][256];  // leader: cluster-wide digit histograms: head select 0..3, full select 4..10
   __shared__ int s_cnt[4];          // leader: n_valid, nan
   __shared__ int s_sel[kClusterSizeMax];  // leader: selected count of each CTA
@@ -249,6 +260,75 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     return (int)cnt == k_rem;
   };
 
+  // ---- one-pass head selection: every CTA counts its valid scores per linear bin in its own shared memory, then
+  //      every CTA sums all the cluster's tables (DSMEM reads, no remote atomics) and scans them from the top: the
+  //      head is everything in the highest bins that together hold at most `cap` candidates.  Returns false when
+  //      that is fewer than 3/4 of cap (scores crowded into one bin): the caller falls back to the exact radix select. ----
+  auto cluster_bin_select = [&](int cap, u64* T_out, int* m_out) -> bool {
+    for (int i = tid; i < kHeadBins; i += blockDim.x) s_bins[i] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const u32 key = rk[i];
+      if (key != 0u) atomicAdd(&s_bins[head_bin_of_key(key)], 1u);
+    }
+    __syncthreads();
+    if (tid < kHeadBins / 2) s_pack[tid] = s_bins[2 * tid] | (s_bins[2 * tid + 1] << 16);  // bins 2t (low half), 2t+1
+    cluster.sync();
+    // this thread's two bins, descending: hi = kHeadBins-1 - 2*tid, lo = hi - 1   (threads below kHeadBins / 2).
+    // DSMEM moves only ~10-20 B per clock per SM, so the tables travel as 16-bit counts (a CTA holds < 65536 keys).
+    const bool owner = tid < kHeadBins / 2;
+    u32 c_hi = 0, c_lo = 0;
+    if (owner) {
+      for (int r0 = 0; r0 < csize; r0 += 8) {  // eight remote loads in flight; start at the own table and go round,
+        u32 v[8];                              // so that no CTA is read by all the others at once
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          const int o = rank + r0 + r, src = o < csize ? o : o - csize;
+          v[r] = 0u;
+          if (r0 + r < csize) v[r] = cluster.map_shared_rank(s_pack, src)[kHeadBins / 2 - 1 - tid];
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          c_lo += v[r] & 0xffffu;
+          c_hi += v[r] >> 16;
+        }
+      }
+    }
+    u32 incl = c_hi + c_lo;
+    for (int o = 1; o < 32; o <<= 1) {
+      const u32 v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_hist[warp] = incl;
+    __syncthreads();
+    u32 wincl = s_hist[lane];
+    for (int o = 1; o < 32; o <<= 1) {
+      const u32 v = __shfl_up_sync(0xffffffffu, wincl, o);
+      if (lane >= o) wincl += v;
+    }
+    const u32 before = __shfl_sync(0xffffffffu, wincl, (warp + 31) & 31);
+    const u32 S_lo = (warp > 0 ? before : 0u) + incl, S_hi = S_lo - c_lo;  // candidates in this bin and above
+    const int q = __syncthreads_count(owner && S_hi <= (u32)cap) + __syncthreads_count(owner && S_lo <= (u32)cap);
+    if (q > 0) {
+      if (2 * tid == q - 1) {
+        s_st[0] = (u32)(kHeadBins - 1 - 2 * tid);
+        s_st[1] = S_hi;
+      }
+      if (2 * tid + 1 == q - 1) {
+        s_st[0] = (u32)(kHeadBins - 2 - 2 * tid);
+        s_st[1] = S_lo;
+      }
+    }
+    __syncthreads();
+    const int bin_t = (int)s_st[0], m = (int)s_st[1];
+    __syncthreads();
+    if (q == 0 || 4 * m < 3 * cap) return false;
+    *T_out = bin_t == 0 ? (1ull << 32) : ((u64)score_key32((float)bin_t * (1.0f / (float)kHeadBins)) << 32);
+    *m_out = m;
+    return true;
+  };
+
   // ---- compact the k_sel selected composites into the leader's sort buffer (DSMEM stores), let the
   //      leader order them by (score desc, row index ASC) -- nms.py:19 re-sorts the already descending list,
   //      which reverses runs of equal scores -- and re-decode them, spread over all CTAs, into processing order ----
@@ -340,21 +420,32 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   wk.fin = 0;
   wk.stripes_done = 0;
 
-  // ---- head: select + sort + walk the first k1 candidates ----
+  // ---- head: select + sort + walk about the first k1 candidates ----
   bool head_ok = false;
+  int m_head = 0;  // candidates in the sorted head
   if (k1 > 0) {
     u64 T = 1ull << 32;  // every valid composite
-    head_ok = (k1 == n_valid) ? true : cluster_select(k1, 0, false, &T);
+    if (k1 == n_valid) {
+      head_ok = true;
+      m_head = k1;
+    } else if (cluster_bin_select(k1, &T, &m_head)) {
+      head_ok = true;
+    } else {
+      head_ok = cluster_select(k1, 0, false, &T);
+      m_head = k1;
+    }
     MXR_STAMP(3);
     if (head_ok) {
-      sort_and_redecode(k1, T, 4);
+      sort_and_redecode(m_head, T, 4);
       MXR_STAMP(6);
-      wk.walk(cluster, 0, k1);
+      // while more candidates follow the head only whole stripes of it are walked, so that the full list (of which
+      // the head is a prefix) can take over at a stripe boundary
+      wk.walk(cluster, 0, m_head < k ? (m_head / kCW) * kCW : m_head);
     }
   }
   // ---- full list, only if the head did not settle the image ----
   int full_path = 0;
-  if (k > 0 && !wk.fin && (!head_ok || k1 < k)) {
+  if (k > 0 && !wk.fin && (!head_ok || m_head < k)) {
     full_path = 1;
     u64 T = 1ull << 32;
     if (k < n_valid) cluster_select(k, 4, true, &T);
