@@ -224,3 +224,20 @@ def test_two_handles_share_kernel_attributes():
     assert np.array_equal(first["rois"], again["rois"]) and np.array_equal(first["keep"], again["keep"])
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("cfgname,lo,width", [("tiny", 0.7, 5e-4), ("voc_test", 0.9990, 9e-4), ("voc_test", 0.25, 0.5)])
+def test_head_selection_when_scores_crowd_few_bins(cfgname, lo, width):
+    """The head is normally cut at a linear score-bin boundary found in one pass; when the scores crowd into one
+    bin (first two cases: all of them inside 1/1024) the kernel falls back to the exact radix select.  Same results
+    either way: equal to the oracle."""
+    cfg = synth.CONFIGS[cfgname]
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(81, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    fg = (lo + cls[0, A:].astype(np.float64) * width).astype(np.float32)  # same order, squeezed into [lo, lo + width)
+    cls[0, A:] = fg
+    cls[0, :A] = 1 - fg
+    out = run(cls, box, info, cfg, rng=np.random.RandomState(0))
+    st = restate.proposal_stages(cls, box, info, cfg["feat_stride"], cfg["scales"], cfg["ratios"], False, cfg["pre"],
+                                 cfg["post"], cfg["thresh"], cfg["min_size"], nms_stop_after=cfg["post"])
+    check_against(st, out, cfg["post"])
