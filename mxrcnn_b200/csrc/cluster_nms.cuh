@@ -136,28 +136,33 @@ __device__ __forceinline__ u32 tile_bits16(const typename Ar<T>::Box rb, T rarea
   return bits;
 }
 
-// Greedy walk of one stripe whose bit rows already sit in shared memory.  Whole CTA.
+// Greedy walk of one stripe whose bit rows already sit in shared memory.  ONE WARP, no block barriers: the
+// suppression words of the stripe's (at most four) 64-box blocks live in registers, each lane owns rows
+// `lane` and `lane + 32` of the current block.
 // Diagonal tiles hold their LOWER triangle (bit j of row i, j < i: "j suppresses i"; the IoU predicate is
 // symmetric bit for bit), off-diagonal words hold "row suppresses column".
 // Returns the new kept count; *fin_out != 0 when the quota was reached.
-__device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_removed, int rows, int c0, int nk, int max_keep,
-                                              int* kept_slot, u64* s_keptbits, int* s_finish, int* fin_out) {
-  const int tid = threadIdx.x;
+__device__ __forceinline__ int scan_rows_warp(const u64* sM, int pitch, const u64* s_removed, int rows, int c0, int nk,
+                                              int max_keep, int* kept_slot, int* fin_out) {
+  const int lane = threadIdx.x & 31;
   const int nblk = (rows + 63) >> 6;
+  u64 rem[kCSW];
+#pragma unroll
+  for (int w = 0; w < kCSW; ++w) rem[w] = s_removed[w];
   int finished = 0;
-  for (int blk = 0; blk < nblk; ++blk) {
-    __syncthreads();
-    if (tid < 32) {
-      const u64 word0 = s_removed[blk];
+#pragma unroll
+  for (int blk = 0; blk < kCSW; ++blk) {
+    if (blk < nblk && !finished) {
       const int nvalid = min(64, rows - blk * 64);
       const u64 valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1ull);
-      const u64 alive = ~word0 & valid;
+      const u64 alive = ~rem[blk] & valid;
+      const int r0 = blk * 64 + lane, r1 = r0 + 32;
       // Greedy keep is the unique fixed point of  keep_i = alive_i and no kept j < i suppresses i ;
       // iterating from keep = alive fixes at least one more leading position per round, and in practice
       // converges in a handful of rounds instead of a 64-step dependent chain.
-      const u64 m0 = ((blk * 64 + tid < rows) ? sM[(blk * 64 + tid) * pitch + blk] : 0ull) & ((1ull << tid) - 1ull);
-      const u64 m1 = ((blk * 64 + 32 + tid < rows) ? sM[(blk * 64 + 32 + tid) * pitch + blk] : 0ull) & ((1ull << (tid + 32)) - 1ull);
-      const bool a0 = (alive >> tid) & 1ull, a1 = (alive >> (tid + 32)) & 1ull;
+      const u64 m0 = (r0 < rows ? sM[r0 * pitch + blk] : 0ull) & ((1ull << lane) - 1ull);
+      const u64 m1 = (r1 < rows ? sM[r1 * pitch + blk] : 0ull) & ((1ull << (lane + 32)) - 1ull);
+      const bool a0 = (alive >> lane) & 1ull, a1 = (alive >> (lane + 32)) & 1ull;
       u64 keep = alive;
       for (int it = 0; it < 64; ++it) {
         const u32 k0 = __ballot_sync(0xffffffffu, a0 && (m0 & keep) == 0ull);
@@ -167,7 +172,6 @@ __device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_r
         keep = nxt;
       }
       u64 kept = keep;
-      int fin = 0;
       if (max_keep > 0 && nk + __popcll(kept) >= max_keep) {
         int want = max_keep - nk;
         u64 k2 = 0, rest = kept;
@@ -178,32 +182,25 @@ __device__ __forceinline__ int scan_rows_smem(const u64* sM, int pitch, u64* s_r
           --want;
         }
         kept = k2;
-        fin = 1;
+        finished = 1;
       }
-      if (tid == 0) {
-        *s_keptbits = kept;
-        *s_finish = fin;
+      const bool k0 = (kept >> lane) & 1ull, k1 = (kept >> (lane + 32)) & 1ull;
+      if (k0) kept_slot[nk + __popcll(kept & ((1ull << lane) - 1ull))] = c0 + r0;
+      if (k1) kept_slot[nk + __popcll(kept & ((1ull << (lane + 32)) - 1ull))] = c0 + r1;
+      nk += __popcll(kept);
+      if (!finished) {
+#pragma unroll
+        for (int w = 0; w < kCSW; ++w) {
+          if (w > blk && w < nblk) {  // boxes kept in this block suppress columns of the later blocks
+            const u64 v = (k0 ? sM[r0 * pitch + w] : 0ull) | (k1 ? sM[r1 * pitch + w] : 0ull);
+            const u32 vlo = __reduce_or_sync(0xffffffffu, (u32)v);
+            const u32 vhi = __reduce_or_sync(0xffffffffu, (u32)(v >> 32));
+            rem[w] |= ((u64)vhi << 32) | vlo;
+          }
+        }
       }
-    }
-    __syncthreads();
-    const u64 kept = *s_keptbits;
-    const int fin = *s_finish;
-    if (tid < 64 && ((kept >> tid) & 1ull)) kept_slot[nk + __popcll(kept & ((1ull << tid) - 1ull))] = c0 + blk * 64 + tid;
-    nk += __popcll(kept);
-    if (fin) {
-      finished = 1;
-      break;
-    }
-    const int nw = nblk - blk - 1;
-    const int w = tid >> 6, row = tid & 63;
-    if (w < nw) {
-      const u64 v = ((kept >> row) & 1ull) ? sM[(blk * 64 + row) * pitch + blk + 1 + w] : 0ull;
-      const u32 vlo = __reduce_or_sync(0xffffffffu, (u32)v);
-      const u32 vhi = __reduce_or_sync(0xffffffffu, (u32)(v >> 32));
-      if ((tid & 31) == 0 && (vlo | vhi)) atomicOr(&s_removed[blk + 1 + w], ((u64)vhi << 32) | vlo);
     }
   }
-  __syncthreads();
   *fin_out = finished;
   return nk;
 }
@@ -266,6 +263,22 @@ struct StripeWalker {
           const int col0 = c0 + cb * 64 + qd * 16;
           if (col0 >= c1) continue;
           const int ncols = min(16, c1 - col0);
+          // this lane's row box is requested BEFORE the column boxes are staged, so that the two L2 round trips overlap
+          const int rt = half * 32 + lane;           // tri: row inside the 64x64 tile
+          const int rl = rb * 64 + rt;               //      row inside the stripe
+          const int kidx = rc * 32 + lane;           // cross: index into the kept list
+          int row = -1;
+          if (tri) {
+            if (c0 + rl < c1) row = c0 + rl;
+          } else if (kidx < nk) {
+            row = __ldcg(kept_slot + kidx);
+          }
+          typename Ar<T>::Box rbox = typename Ar<T>::Box();
+          T rarea = T(0);
+          if (row >= 0) {
+            rbox = ldcg_box<T>(box + row);
+            rarea = __ldcg(area + row);
+          }
           __syncwarp();
           if (lane < ncols) {
             t_box[lane] = ldcg_box<T>(box + col0 + lane);
@@ -273,34 +286,28 @@ struct StripeWalker {
           }
           __syncwarp();
           if (tri) {
-            const int rt = half * 32 + lane;           // row inside the 64x64 tile
-            const int rl = rb * 64 + rt;               // row inside the stripe
-            const int row = c0 + rl;
-            if (row < c1) {
+            if (row >= 0) {
               int je = ncols;
               if (rb == cb) je = min(ncols, max(0, rt - qd * 16));   // diagonal tile: strictly BELOW the diagonal
-              const u32 bits = tile_bits16<T>(ldcg_box<T>(box + row), __ldcg(area + row), t_box, t_area, 0, je, thr, thr_lo, thr_hi);
+              const u32 bits = tile_bits16<T>(rbox, rarea, t_box, t_area, 0, je, thr, thr_lo, thr_hi);
               reinterpret_cast<unsigned short*>(L_sM + rl * kCPitch + cb)[qd] = (unsigned short)bits;
             }
           } else {
             u32 bits = 0;
-            const int kidx = rc * 32 + lane;
-            if (kidx < nk) {
-              const int slot = __ldcg(kept_slot + kidx);
-              bits = tile_bits16<T>(ldcg_box<T>(box + slot), __ldcg(area + slot), t_box, t_area, 0, ncols, thr, thr_lo, thr_hi);
-            }
+            if (row >= 0) bits = tile_bits16<T>(rbox, rarea, t_box, t_area, 0, ncols, thr, thr_lo, thr_hi);
             bits = __reduce_or_sync(0xffffffffu, bits);
             if (lane == 0 && bits) atomicOr(reinterpret_cast<u32*>(L_removed + cb) + (qd >> 1), bits << (16 * (qd & 1)));
           }
         }
       }
       cluster.sync();
-      if (rank == 0) {
+      if (rank == 0 && warp == 0) {  // the leader's first warp walks the stripe; everybody else waits at the barrier
         int f = 0;
-        nk = scan_rows_smem(sM, kCPitch, s_removed, c1 - c0, c0, nk, max_keep, kept_slot, s_keptbits, s_finish, &f);
-        if (tid < kCSW) s_removed[tid] = 0ull;
-        if (tid == 0) {
-          s_status[0] = nk;
+        const int nk2 = scan_rows_warp(sM, kCPitch, s_removed, c1 - c0, c0, nk, max_keep, kept_slot, &f);
+        __syncwarp();
+        if (lane < kCSW) s_removed[lane] = 0ull;
+        if (lane == 0) {
+          s_status[0] = nk2;
           s_status[1] = f;
         }
       }

@@ -228,9 +228,10 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
     cl.a = ca.a;
     cl.o = ca.o;
     cl.ctrl = L.ctrl;
-    cl.dbg = L.dbg;
-    h->dbg_ptr = L.dbg;
-    h->dbg_images = L.B;
+    // phase time stamps (%globaltimer reads on the leader's critical path) only while profiling is switched on
+    cl.dbg = h->prof_on ? L.dbg : nullptr;
+    h->dbg_ptr = cl.dbg;
+    h->dbg_images = cl.dbg ? L.B : 0;
     const size_t smem_c = cluster_smem_bytes(sort_cap);
     // Cluster size per call.  A wide cluster shortens every phase of one image (measured per wave at 38x63x9:
     // 47 / 50 / 54 / 58 / 72 / 98 us for 16 / 12 / 8 / 6 / 4 / 2 CTAs) but fewer of them are resident at once

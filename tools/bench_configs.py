@@ -58,6 +58,11 @@ def proposal_row(name, B=8, steps=50):
     e1.record(st)
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / steps * 1e3
+    h.profile_enable(True)
+    for _ in range(3):
+        step()
+    h.profile_read()
+    h.profile_enable(False)
     ph = h.proposal_phase_times()
     t_cpu = wall(lambda: restate.proposal_stages(cls[:1], box[:1], info[:1], cfg["feat_stride"], cfg["scales"], cfg["ratios"],
                                                  False, cfg["pre"], post, cfg["thresh"], cfg["min_size"],
