@@ -353,11 +353,12 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       if (tid == 0) L_sel[rank] = s_local[0];
     }
     cluster.sync();
-    if (tid == 0) {
-      int off = 0;
-      for (int r = 0; r < rank; ++r) off += L_sel[r];
-      s_local[1] = off;   // base of this CTA inside the sort buffer
-      s_local[0] = 0;     // running position inside this CTA
+    if (warp == 0) {  // one DSMEM round trip: the lower ranks' counts are fetched by separate lanes
+      const int off = __reduce_add_sync(0xffffffffu, lane < rank ? L_sel[lane] : 0);
+      if (lane == 0) {
+        s_local[1] = off;   // base of this CTA inside the sort buffer
+        s_local[0] = 0;     // running position inside this CTA
+      }
     }
     __syncthreads();
 #pragma unroll

@@ -7,6 +7,7 @@ from mxrcnn_b200.rcnn.rpn.proposal import proposal_forward
 cfg = synth.CONFIGS["voc_test"]
 anchors = generate_anchors(16.0, list(cfg["ratios"]), np.array(cfg["scales"], dtype=float))
 h = _lib.Handle(0)
+h.profile_enable(True)
 c, b, i = (torch.from_numpy(x).cuda() for x in synth.proposal_batch(range(3, 11), cfg))
 acc = {}
 for it in range(30):
