@@ -127,7 +127,7 @@ def run_reference_arm(args, rank, world):
                                    "+ helper/processing/nms.py), one worker process per image" % (steps, per_step)},
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # -----------------------------------------------------------------------------------------
@@ -213,8 +213,9 @@ def run_gpu_arm(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     dist = None
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version there)
+        # stdout carries the ONE JSON line: whatever NCCL logs (its version banner at any NCCL_DEBUG level, INFO
+        # traces when the caller asks for them) goes to a per-process file instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/mxrcnn_b200_nccl_%h_%p.log")
         import torch.distributed as dist_mod
         dist = dist_mod
         dist.init_process_group("nccl", device_id=dev)
@@ -506,8 +507,8 @@ def run_gpu_arm(args, rank, world, local_rank):
             bytes_launch = alg.get(dom, alg["op"]) / max(1.0, 1.0)
             ach = bytes_launch / per_launch_s / 1e9
             # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel at this
-            # configuration (profiles/r01f_cluster_kernel_ncu.md); not re-measured here (never time under a profiler)
-            traffic = 3554560 if (dom == "proposal_cluster_kernel" and B == 8 and CONFIG == "voc_test") else None
+            # configuration (profiles/r01g_cluster_kernel_ncu.md); not re-measured here (never time under a profiler)
+            traffic = 3576576 if (dom == "proposal_cluster_kernel" and B == 8 and CONFIG == "voc_test") else None
             roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                     "us_per_launch": d["us_per_launch"], "share_of_step": d["share"]}
@@ -560,13 +561,35 @@ def run_gpu_arm(args, rank, world, local_rank):
                                        "process per core" % n_cpu},
             "parity_spot_check": ok, "allgather_checksum": checksum,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its version banner on stdout),
+    so file descriptor 1 is pointed at stderr for the rest of the run and the line goes to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
