@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   __shared__ u32 s_hist[256];
   __shared__ u32 s_bins[kHeadBins];      // this CTA's counts of its valid scores per linear score bin (head selection)
   __shared__ u32 s_pack[kHeadBins / 2];  // the same as pairs of 16-bit counts: what the other CTAs read
+  __shared__ u32 s_cursor[kHeadBins];    // fill level of each bin's bucket while the head is ordered
   __shared__ u32 s_ghist[12][256];  // leader: cluster-wide digit histograms: head select 0..3, full select 4..10
   __shared__ int s_cnt[4];          // leader: n_valid, nan
   __shared__ int s_sel[kClusterSizeMax];  // leader: selected count of each CTA
@@ -309,6 +310,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     }
     const u32 before = __shfl_sync(0xffffffffu, wincl, (warp + 31) & 31);
     const u32 S_lo = (warp > 0 ? before : 0u) + incl, S_hi = S_lo - c_lo;  // candidates in this bin and above
+    if (owner) {  // the local counts are spent: the table now holds, per bin, how many candidates sit in HIGHER bins
+      s_bins[kHeadBins - 1 - 2 * tid] = S_hi - c_hi;
+      s_bins[kHeadBins - 2 - 2 * tid] = S_lo - c_lo;
+    }
     const int q = __syncthreads_count(owner && S_hi <= (u32)cap) + __syncthreads_count(owner && S_lo <= (u32)cap);
     if (q > 0) {
       if (2 * tid == q - 1) {
@@ -327,6 +332,97 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     *T_out = bin_t == 0 ? (1ull << 32) : ((u64)score_key32((float)bin_t * (1.0f / (float)kHeadBins)) << 32);
     *m_out = m;
     return true;
+  };
+
+  // ---- head of at most 1024 candidates: order it WITHOUT a sort.  Every CTA compacts its own selected composites
+  //      locally, pulls everybody's into its shared memory (one DSMEM load per thread), and counts for each of its
+  //      own composites how many are greater: that count is the composite's position in (score desc, row index ASC)
+  //      order -- nms.py:19 re-sorts the already descending list, which reverses runs of equal scores.  The owner
+  //      then decodes the box straight into that position.  ~1M comparisons spread over the cluster's threads
+  //      instead of a 55-stage bitonic network on one SM followed by a separate re-decode pass. ----
+  auto rank_and_redecode = [&](int k_sel, u64 T, int stamp, bool binned) {
+    const bool need_p = (u32)T != 0u;  // the threshold cuts inside a run of equal scores
+    auto selected = [&](int i) -> bool {
+      const u32 key = rk[i];
+      if (key == 0u) return false;
+      const u64 c = ((u64)key << 32) | ((need_p && key == (u32)(T >> 32)) ? p_of_item(i) : 0xffffffffu);
+      return c >= T;
+    };
+    u64* loc = sM;       // this CTA's selected composites, unordered (the bit-row area is free until the NMS walk)
+    u64* all = sortbuf;  // this CTA's copy of all k_sel composites
+    __syncthreads();
+    if (tid == 0) s_local[0] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const bool sel = selected(i);
+      const u32 m = __ballot_sync(0xffffffffu, sel);
+      int base = 0;
+      if (lane == 0 && m) base = atomicAdd(&s_local[0], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (sel) loc[base + __popc(m & ((1u << lane) - 1u))] = ((u64)rk[i] << 32) | (u32)(~p_of_item(i));
+    }
+    cluster.sync();  // every CTA's list and count are in place
+    MXR_STAMP(stamp);
+    if (warp == 0) {  // offsets of the CTAs' lists inside `all`
+      const int cnt = lane < csize ? cluster.map_shared_rank(s_local, lane)[0] : 0;
+      int incl = cnt;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane < kClusterSizeMax) s_sel[lane] = incl - cnt;
+    }
+    if (binned)
+      for (int i = tid; i < kHeadBins; i += blockDim.x) s_cursor[i] = 0;
+    __syncthreads();
+    for (int j = tid; j < k_sel; j += blockDim.x) {  // one remote load per thread
+      int r = 0;
+      while (r + 1 < csize && s_sel[r + 1] <= j) ++r;
+      const u64 c = cluster.map_shared_rank(loc, r)[j - s_sel[r]];
+      int slot = j;
+      if (binned) {  // bucket by score bin: s_bins[bin] candidates sit in higher bins (cluster_bin_select)
+        const int bin = head_bin_of_key((u32)(c >> 32));
+        slot = (int)(s_bins[bin] + atomicAdd(&s_cursor[bin], 1u));
+      }
+      all[slot] = c;
+    }
+    __syncthreads();
+    const int n_loc = s_local[0];
+    int G = 32;  // threads per own composite
+    while (G > 1 && n_loc * G > (int)blockDim.x) G >>= 1;
+    for (int i0 = 0; i0 < n_loc; i0 += blockDim.x / G) {
+      const int i = i0 + tid / G, sub = tid & (G - 1);
+      const u64 mine = i < n_loc ? loc[i] : ~0ull;
+      int pos = 0;
+      if (i < n_loc) {
+        int lo = 0, n_cmp = k_sel;  // only the own bucket has to be looked at when the copy is bucketed
+        if (binned) {
+          const int bin = head_bin_of_key((u32)(mine >> 32));
+          lo = (int)s_bins[bin];
+          n_cmp = (int)s_cursor[bin];
+        }
+        for (int j = sub; j < n_cmp; j += G) pos += all[lo + j] > mine ? 1 : 0;
+        if (sub == 0) pos += lo;
+      }
+      for (int o = 1; o < G; o <<= 1) pos += __shfl_xor_sync(0xffffffffu, pos, o);
+      if (sub == 0 && i < n_loc) {
+        const int p = (int)(~(u32)mine);
+        const int a = p % dg.A, r = p / dg.A;
+        const int h = r / dg.wc, w = r - h * dg.wc;
+        double bx[4];
+        decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx);
+        const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
+        const float s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
+        const size_t o = (size_t)b * g.a.cap + pos;
+        const_cast<double4*>(g.a.box)[o] = make_double4(bx[0], bx[1], bx[2], bx[3]);
+        const_cast<double*>(g.a.area)[o] = box_area<double>(bx[0], bx[1], bx[2], bx[3]);
+        const_cast<float*>(g.a.score)[o] = s;
+        const_cast<int*>(g.a.orig)[o] = p;
+      }
+    }
+    MXR_STAMP(stamp + 1);
+    cluster.sync();  // the boxes are visible to every CTA of the cluster; nobody reads `loc` any more
   };
 
   // ---- compact the k_sel selected composites into the leader's sort buffer (DSMEM stores), let the
@@ -424,6 +520,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   // ---- head: select + sort + walk about the first k1 candidates ----
   bool head_ok = false;
   int m_head = 0;  // candidates in the sorted head
+  bool head_binned = false;  // the head was cut at a score-bin boundary
   if (k1 > 0) {
     u64 T = 1ull << 32;  // every valid composite
     if (k1 == n_valid) {
@@ -431,13 +528,15 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       m_head = k1;
     } else if (cluster_bin_select(k1, &T, &m_head)) {
       head_ok = true;
+      head_binned = true;
     } else {
       head_ok = cluster_select(k1, 0, false, &T);
       m_head = k1;
     }
     MXR_STAMP(3);
     if (head_ok) {
-      sort_and_redecode(m_head, T, 4);
+      if (m_head <= 1024) rank_and_redecode(m_head, T, 4, head_binned);
+      else sort_and_redecode(m_head, T, 4);
       MXR_STAMP(6);
       // while more candidates follow the head only whole stripes of it are walked, so that the full list (of which
       // the head is a prefix) can take over at a stripe boundary
