@@ -1,5 +1,7 @@
+"""Mean phase times of the fused proposal kernel (its own %globaltimer stamps) on one batch of 8 L2-resident images.
+Used with temporary extra stamps to time sub-phases while tuning; python tools/phase_probe.py"""
 import os, sys, numpy as np, torch
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import synth
 from mxrcnn_b200 import _lib
 from mxrcnn_b200.helper.processing.generate_anchor import generate_anchors
