@@ -100,6 +100,8 @@ int mxr_create(int device, mxr_handle_t* out) {
   h->no_cluster = (nc && nc[0] == '1') ? 1 : 0;
   const char* c8 = getenv("MXRCNN_B200_CLUSTER8");
   h->cluster_override = (c8 && c8[0] == '1') ? 8 : 0;
+  const char* np = getenv("MXRCNN_B200_NO_PDL");
+  h->no_pdl = (np && np[0] == '1') ? 1 : 0;
   const char* cs = getenv("MXRCNN_B200_CLUSTER");
   if (cs) {
     const int v = atoi(cs);

@@ -102,6 +102,7 @@ struct Handle {
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
   int cluster_override; // MXRCNN_B200_CLUSTER=2|4|8|16 pins the cluster size of the fused proposal kernel (tests cover
                         // them all); MXRCNN_B200_CLUSTER8=1 is the older spelling of 8.  0: chosen per call
+  int no_pdl;           // MXRCNN_B200_NO_PDL=1: launch the fused kernel without programmatic dependent launch
   unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
   int dbg_images;
   cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path

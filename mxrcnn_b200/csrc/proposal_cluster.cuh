@@ -117,6 +117,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     if (tid < 2) s_status[tid] = 0;
   }
   if (tid < 4) s_local[tid] = 0;
+  // programmatic dependent launch (proposal.cu): let the next kernel of the stream be scheduled, then wait until
+  // everything launched before this kernel has completed and its writes are visible (no-ops for a plain launch)
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   MXR_STAMP(0);
   cluster.sync();
   MXR_STAMP(1);
