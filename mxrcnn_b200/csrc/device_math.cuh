@@ -84,10 +84,13 @@ __device__ __forceinline__ int iou_band(T ax1, T ay1, T ax2, T ay2, T aarea, T b
   const T xx1 = A::vmax(ax1, bx1), yy1 = A::vmax(ay1, by1);
   const T xx2 = A::vmin(ax2, bx2), yy2 = A::vmin(ay2, by2);
   const T w0 = A::add(A::sub(xx2, xx1), T(1)), h0 = A::add(A::sub(yy2, yy1), T(1));
-  const T w = w0 > T(0) ? w0 : T(0), h = h0 > T(0) ? h0 : T(0);
-  const T inter = A::mul(w, h);
+  // max(0, w0) * max(0, h0) without the two clamps (the compiler expands `x > 0 ? x : 0` on doubles into a NaN-quieting
+  // max of ~8 instructions): the product is +0 as soon as one extent is <= 0.  That differs from the clamped
+  // form only when the other extent is infinite or NaN (0 * inf), and then an area, hence `uni`, is infinite or NaN
+  // too: such pairs are sent to the exact evaluation by the `finite` test below.
+  const T inter = (w0 > T(0) && h0 > T(0)) ? A::mul(w0, h0) : T(0);
   const T uni = A::sub(A::add(aarea, barea), inter);
-  const bool pos = uni > T(0);
+  const bool pos = uni > T(0) && uni <= (sizeof(T) == 8 ? T(1.7976931348623157e308) : T(3.4028234663852886e38f));
   const bool keep = inter <= A::mul(thr_lo, uni);
   const bool supp = inter >= A::mul(thr_hi, uni);
   return !pos ? 2 : (keep ? 0 : (supp ? 1 : 2));
