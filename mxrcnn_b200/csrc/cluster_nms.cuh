@@ -120,12 +120,20 @@ __device__ __forceinline__ u32 tile_bits16(const typename Ar<T>::Box rb, T rarea
                                            const T* careas, int j_begin, int j_end, T thr, T thr_lo, T thr_hi) {
   u32 bits = 0;
   if (thr > T(0)) {
+    // branch-free pass over the columns; the rare undecided pairs (inside the band, degenerate) are settled afterwards
+    u32 undecided = 0;
 #pragma unroll 4
     for (int j = j_begin; j < j_end; ++j) {
       const typename Ar<T>::Box cb = cols[j];
-      int r = iou_band<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr_lo, thr_hi);
-      if (r == 2) r = iou_exceeds<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr) ? 1 : 0;
-      bits |= (u32)r << j;
+      const int r = iou_band<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr_lo, thr_hi);
+      bits |= (u32)(r & 1) << j;
+      undecided |= (u32)(r >> 1) << j;
+    }
+    while (undecided) {
+      const int j = __ffs(undecided) - 1;
+      undecided &= undecided - 1u;
+      const typename Ar<T>::Box cb = cols[j];
+      if (iou_exceeds<T>(rb.x, rb.y, rb.z, rb.w, rarea, cb.x, cb.y, cb.z, cb.w, careas[j], thr)) bits |= 1u << j;
     }
   } else {
     for (int j = j_begin; j < j_end; ++j) {
