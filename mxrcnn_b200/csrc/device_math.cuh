@@ -114,6 +114,18 @@ struct DecodeGeom {
   double fs;       // feat stride
 };
 
+// max(min(v, lim), 0) of bbox_transform.py:86-94 as two compare-selects.  The library fmin / fmax cost ~8
+// instructions each on sm_100 (NaN quieting), and the compiler turns `x > 0.0 ? x : 0.0` into the same sequence, so
+// the selects are spelled on the 32-bit halves.  Same values as fmax(fmin(v, lim), 0.0), including NaN -> lim and
+// -0.0 -> +0.0 (the NaN check of proposal.py:61 looks at the raw deltas, not at the clipped boxes).
+__device__ __forceinline__ double select_f64(bool p, double a, double b) {
+  return __hiloint2double(p ? __double2hiint(a) : __double2hiint(b), p ? __double2loint(a) : __double2loint(b));
+}
+__device__ __forceinline__ double clip_0_lim(double v, double lim) {
+  const double t = select_f64(v < lim, v, lim);
+  return select_f64(t > 0.0, t, 0.0);
+}
+
 // rcnn/rpn/proposal.py:77-113 + helper/processing/bbox_transform.py:35-96 for ONE anchor.
 // (h, w, a) index the cropped map; deltas are read from the full (4A,H,W) map of the image.
 // f64 arithmetic, exp in f32 (numpy evaluates np.exp on the f32 deltas), clip limits are
@@ -146,10 +158,10 @@ __device__ __forceinline__ void decode_clip(const AnchorTable& at, const DecodeG
   const double hy = A::mul(0.5, A::sub(ph, 1.0));
   const double lim_x = (double)__fsub_rn(im_w, 1.0f);
   const double lim_y = (double)__fsub_rn(im_h, 1.0f);
-  out[0] = fmax(fmin(A::sub(pcx, hx), lim_x), 0.0);
-  out[1] = fmax(fmin(A::sub(pcy, hy), lim_y), 0.0);
-  out[2] = fmax(fmin(A::add(pcx, hx), lim_x), 0.0);
-  out[3] = fmax(fmin(A::add(pcy, hy), lim_y), 0.0);
+  out[0] = clip_0_lim(A::sub(pcx, hx), lim_x);
+  out[1] = clip_0_lim(A::sub(pcy, hy), lim_y);
+  out[2] = clip_0_lim(A::add(pcx, hx), lim_x);
+  out[3] = clip_0_lim(A::add(pcy, hy), lim_y);
 }
 
 // proposal.py:156-161 with min_size*im_info[2] evaluated in f32 (NEP 50) and promoted.
