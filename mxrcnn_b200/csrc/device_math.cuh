@@ -114,6 +114,17 @@ struct DecodeGeom {
   double fs;       // feat stride
 };
 
+// n / d for 0 <= n < 2^24, 1 <= d < 2^24 (anchor indices: A*H*W <= 2^24) through a float reciprocal plus one
+// correction step; `rcp` = 1.0f / d computed once.  An integer division by a run-time value costs ~25 instructions.
+// (float)n is exact, the product is off by < 1 in the quotient, so one step of correction suffices.
+__device__ __forceinline__ int fast_div(int n, int d, float rcp) {
+  int q = (int)((float)n * rcp);
+  const int r = n - q * d;
+  q += (r >= d) ? 1 : 0;
+  q -= (r < 0) ? 1 : 0;
+  return q;
+}
+
 // max(min(v, lim), 0) of bbox_transform.py:86-94 as two compare-selects.  The library fmin / fmax cost ~8
 // instructions each on sm_100 (NaN quieting), and the compiler turns `x > 0.0 ? x : 0.0` into the same sequence, so
 // the selects are spelled on the 32-bit halves.  Same values as fmax(fmin(v, lim), 0.0), including NaN -> lim and

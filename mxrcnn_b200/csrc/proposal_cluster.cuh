@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   const int chunk = (pg.n_crop + csize - 1) / csize;
   const int q_begin = rank * chunk;
   const int q_end = min(q_begin + chunk, pg.n_crop);
+  const float rcp_hwc = 1.0f / (float)hwc, rcp_wc = 1.0f / (float)dg.wc, rcp_A = 1.0f / (float)dg.A;
   u32 rk[ITEMS];
   {
     int nvalid = 0, nnan = 0;
@@ -143,8 +144,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       u32 key = 0;
       bool nan = false;
       if (q < q_end) {
-        const int a = q / hwc, r = q - a * hwc;
-        const int h = r / dg.wc, w = r - h * dg.wc;
+        const int a = fast_div(q, hwc, rcp_hwc), r = q - a * hwc;
+        const int h = fast_div(r, dg.wc, rcp_wc), w = r - h * dg.wc;
         double bx[4];
         bool dnan;
         decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx, &dnan);
@@ -412,11 +413,11 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       for (int o = 1; o < G; o <<= 1) pos += __shfl_xor_sync(0xffffffffu, pos, o);
       if (sub == 0 && i < n_loc) {
         const int p = (int)(~(u32)mine);
-        const int a = p % dg.A, r = p / dg.A;
-        const int h = r / dg.wc, w = r - h * dg.wc;
+        const int r = fast_div(p, dg.A, rcp_A), a = p - r * dg.A;
+        const int h = fast_div(r, dg.wc, rcp_wc), w = r - h * dg.wc;
         double bx[4];
         decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx);
-        const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
+        const int a2 = a, w2 = r % dg.W, h2 = r / dg.W;  // the score sits at the flat (H,W,A) index of the FULL map (quirk Q1)
         const float s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
         const size_t o = (size_t)b * g.a.cap + pos;
         const_cast<double4*>(g.a.box)[o] = make_double4(bx[0], bx[1], bx[2], bx[3]);
