@@ -83,11 +83,11 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   __shared__ u32 s_pack[kHeadBins / 2];  // the same as pairs of 16-bit counts: what the other CTAs read
   __shared__ u32 s_cursor[kHeadBins];    // fill level of each bin's bucket while the head is ordered
   __shared__ u32 s_ghist[12][256];  // leader: cluster-wide digit histograms: head select 0..3, full select 4..10
-  __shared__ int s_cnt[4];          // leader: n_valid, nan
   __shared__ int s_sel[kClusterSizeMax];  // leader: selected count of each CTA
   __shared__ int s_status[2];       // leader: kept so far, quota reached
   __shared__ u32 s_st[4];
   __shared__ int s_local[4];
+  __shared__ int s_pub[2];  // this CTA's valid / NaN counts of the decode phase, read by the other CTAs
   __shared__ u64 s_keptbits;
   __shared__ int s_finish;
   cgx::cluster_group cluster = cgx::this_cluster();
@@ -107,12 +107,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   u64* L_sM = cluster.map_shared_rank(sM, 0);
   u64* L_removed = cluster.map_shared_rank(s_removed, 0);
   u32* L_ghist = cluster.map_shared_rank(&s_ghist[0][0], 0);
-  int* L_cnt = cluster.map_shared_rank(s_cnt, 0);
   int* L_sel = cluster.map_shared_rank(s_sel, 0);
   int* L_status = cluster.map_shared_rank(s_status, 0);
   if (rank == 0) {
     for (int i = tid; i < 12 * 256; i += blockDim.x) (&s_ghist[0][0])[i] = 0;
-    if (tid < 4) s_cnt[tid] = 0;
     if (tid < kCSW) s_removed[tid] = 0ull;
     if (tid < 2) s_status[tid] = 0;
   }
@@ -121,8 +119,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   // everything launched before this kernel has completed and its writes are visible (no-ops for a plain launch)
   asm volatile("griddepcontrol.launch_dependents;");
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  // No start-up barrier: nothing touches another CTA's shared memory before the barrier that ends the decode phase.
+  for (int i = tid; i < kHeadBins; i += blockDim.x) s_bins[i] = 0;
+  __syncthreads();
   MXR_STAMP(0);
-  cluster.sync();
   MXR_STAMP(1);
 
   // ---- P1: decode + clip + min-size filter (proposal.py:77-120); keys stay in registers ----
@@ -162,6 +162,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
         key = valid ? score_key32(s) : 0u;
       }
       rk[i] = key;
+      if (key != 0u) atomicAdd(&s_bins[head_bin_of_key(key)], 1u);  // head selection table, see cluster_bin_select
       nvalid += __popc(__ballot_sync(0xffffffffu, key != 0u));
       nnan += __popc(__ballot_sync(0xffffffffu, nan));
     }
@@ -179,15 +180,18 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
       if (nnan) atomicAdd(&s_local[1], nnan);
     }
     __syncthreads();
-    if (tid == 0) {
-      if (s_local[0]) atomicAdd(L_cnt, s_local[0]);
-      if (s_local[1]) atomicAdd(L_cnt + 1, s_local[1]);
-    }
+    if (tid < 2) s_pub[tid] = s_local[tid];
+    if (tid < kHeadBins / 2) s_pack[tid] = s_bins[2 * tid] | (s_bins[2 * tid + 1] << 16);  // bins 2t (low half), 2t+1
   }
-  cluster.sync();
-  if (tid == 0) {
-    s_local[2] = L_cnt[0];
-    s_local[3] = L_cnt[1];
+  cluster.sync();  // ONE barrier ends the decode phase: counts and score-bin tables of every CTA are published
+  if (warp == 0) {  // every CTA sums the published counts itself (one DSMEM round trip, one lane per CTA)
+    const int* pub = cluster.map_shared_rank(s_pub, lane < csize ? lane : 0);
+    const int nv = __reduce_add_sync(0xffffffffu, lane < csize ? pub[0] : 0);
+    const int nn = __reduce_add_sync(0xffffffffu, lane < csize ? pub[1] : 0);
+    if (lane == 0) {
+      s_local[2] = nv;
+      s_local[3] = nn;
+    }
   }
   __syncthreads();
   const int n_valid = s_local[2];
@@ -266,21 +270,12 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     return (int)cnt == k_rem;
   };
 
-  // ---- one-pass head selection: every CTA counts its valid scores per linear bin in its own shared memory, then
-  //      every CTA sums all the cluster's tables (DSMEM reads, no remote atomics) and scans them from the top: the
+  // ---- one-pass head selection: every CTA has counted its valid scores per linear bin in its own shared memory
+  //      (decode loop); every CTA sums all the cluster's tables (DSMEM reads, no remote atomics) and scans them from the top: the
   //      head is everything in the highest bins that together hold at most `cap` candidates.  Returns false when
   //      that is fewer than 3/4 of cap (scores crowded into one bin): the caller falls back to the exact radix select. ----
   auto cluster_bin_select = [&](int cap, u64* T_out, int* m_out) -> bool {
-    for (int i = tid; i < kHeadBins; i += blockDim.x) s_bins[i] = 0;
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const u32 key = rk[i];
-      if (key != 0u) atomicAdd(&s_bins[head_bin_of_key(key)], 1u);
-    }
-    __syncthreads();
-    if (tid < kHeadBins / 2) s_pack[tid] = s_bins[2 * tid] | (s_bins[2 * tid + 1] << 16);  // bins 2t (low half), 2t+1
-    cluster.sync();
+    // the per-CTA tables were filled during the decode loop and published (16-bit pairs) before its closing barrier
     // this thread's two bins, descending: hi = kHeadBins-1 - 2*tid, lo = hi - 1   (threads below kHeadBins / 2).
     // DSMEM moves only ~10-20 B per clock per SM, so the tables travel as 16-bit counts (a CTA holds < 65536 keys).
     const bool owner = tid < kHeadBins / 2;
