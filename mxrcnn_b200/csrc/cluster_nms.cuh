@@ -222,10 +222,9 @@ struct StripeWalker {
   int* kept_slot;                   // global, kept boxes so far
   u64* sM;                          // leader smem: [kCW][kCPitch]
   u64* s_removed;                   // leader smem: [kCSW]
-  int* s_status;                    // leader smem: [2] kept so far, quota reached
+  int* s_status;                    // every CTA: [2] kept so far, quota reached (written by the leader, 8-byte aligned)
   u64* L_sM;
   u64* L_removed;
-  int* L_status;
   typename Ar<T>::Box* t_box;       // this warp's staging: [16]
   T* t_area;
   u64* s_keptbits;
@@ -314,21 +313,14 @@ struct StripeWalker {
         const int nk2 = scan_rows_warp(sM, kCPitch, s_removed, c1 - c0, c0, nk, max_keep, kept_slot, &f);
         __syncwarp();
         if (lane < kCSW) s_removed[lane] = 0ull;
-        if (lane == 0) {
-          s_status[0] = nk2;
-          s_status[1] = f;
-        }
+        // the result goes INTO every CTA's shared memory (one 8-byte remote store per CTA): after the barrier nobody
+        // reads anybody else's shared memory any more, so the kernel needs no closing cluster barrier after a walk
+        if (lane < csize) *reinterpret_cast<int2*>(cluster.map_shared_rank(s_status, lane)) = make_int2(nk2, f);
       }
       cluster.sync();
-      if (tid == 0) {
-        s_local[2] = L_status[0];
-        s_local[3] = L_status[1];
-      }
-      __syncthreads();
-      nk = s_local[2];
-      fin = s_local[3];
+      nk = s_status[0];  // rewritten only after the next stripe's first barrier, which every thread passes after this read
+      fin = s_status[1];
       stripes_done = s + 1;
-      __syncthreads();
     }
   }
 };

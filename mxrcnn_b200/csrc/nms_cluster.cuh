@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(1024, 1) nms_cluster_kernel(NmsClusterArgs<T> 
   namespace cgx = cooperative_groups;
   typedef typename Ar<T>::Box Box;
   extern __shared__ __align__(16) unsigned char dyn_smem[];
-  __shared__ int s_status[2];
+  __shared__ __align__(8) int s_status[2];
   __shared__ int s_local[4];
   __shared__ u64 s_keptbits;
   __shared__ int s_finish;
@@ -119,7 +119,6 @@ __global__ void __launch_bounds__(1024, 1) nms_cluster_kernel(NmsClusterArgs<T> 
   wk.s_status = s_status;
   wk.L_sM = cluster.map_shared_rank(sM, 0);
   wk.L_removed = cluster.map_shared_rank(s_removed, 0);
-  wk.L_status = cluster.map_shared_rank(s_status, 0);
   wk.t_box = t_box;
   wk.t_area = t_area;
   wk.s_keptbits = &s_keptbits;

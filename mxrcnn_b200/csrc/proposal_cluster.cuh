@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   __shared__ u32 s_cursor[kHeadBins];    // fill level of each bin's bucket while the head is ordered
   __shared__ u32 s_ghist[12][256];  // leader: cluster-wide digit histograms: head select 0..3, full select 4..10
   __shared__ int s_sel[kClusterSizeMax];  // leader: selected count of each CTA
-  __shared__ int s_status[2];       // leader: kept so far, quota reached
+  __shared__ __align__(8) int s_status[2];  // kept so far, quota reached: written by the leader into every CTA
   __shared__ u32 s_st[4];
   __shared__ int s_local[4];
   __shared__ int s_pub[2];  // this CTA's valid / NaN counts of the decode phase, read by the other CTAs
@@ -108,7 +108,6 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   u64* L_removed = cluster.map_shared_rank(s_removed, 0);
   u32* L_ghist = cluster.map_shared_rank(&s_ghist[0][0], 0);
   int* L_sel = cluster.map_shared_rank(s_sel, 0);
-  int* L_status = cluster.map_shared_rank(s_status, 0);
   if (rank == 0) {
     for (int i = tid; i < 12 * 256; i += blockDim.x) (&s_ghist[0][0])[i] = 0;
     if (tid < kCSW) s_removed[tid] = 0ull;
@@ -505,7 +504,6 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   wk.s_status = s_status;
   wk.L_sM = L_sM;
   wk.L_removed = L_removed;
-  wk.L_status = L_status;
   wk.t_box = t_box;
   wk.t_area = t_area;
   wk.s_keptbits = &s_keptbits;
@@ -573,7 +571,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
     __syncthreads();
     coop_write_outputs<double>(g.a, g.o, cb, b, wk.nk, k);
   }
-  cluster.sync();  // nobody leaves while its shared memory may still be addressed
+  // Nobody may leave while its shared memory can still be addressed by another CTA.  Every stripe of the walk and every
+  // (re)ordering step ends with a cluster barrier AFTER its last remote access, so a closing barrier is only needed
+  // when neither ran (no valid candidate at all: the last remote access was the count pull after the decode phase).
+  if (wk.stripes_done == 0 && !head_ok && !full_path) cluster.sync();
   MXR_STAMP(8);
   if (g.dbg && rank == 0 && tid == 0) {
     g.dbg[(size_t)b * 16 + 9] = (u64)wk.stripes_done;
