@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(1024, 1) box_head_kernel(BoxHeadArgs g) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const double lim = (q & 1) ? lim_y : lim_x;
-        bx[q] = A::div(A::vmax(A::vmin(bx[q], lim), 0.0), scale);
+        bx[q] = A::div(clip_0_lim(bx[q], lim), scale);
       }
       sbox[i] = make_double4(bx[0], bx[1], bx[2], bx[3]);
       sarea[i] = box_area<double>(bx[0], bx[1], bx[2], bx[3]);
