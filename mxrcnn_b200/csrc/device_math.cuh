@@ -115,13 +115,21 @@ struct DecodeGeom {
 };
 
 // n / d for 0 <= n < 2^24, 1 <= d < 2^24 (anchor indices: A*H*W <= 2^24) through a float reciprocal plus one
-// correction step; `rcp` = 1.0f / d computed once.  An integer division by a run-time value costs ~25 instructions.
-// (float)n is exact, the product is off by < 1 in the quotient, so one step of correction suffices.
+// correction loop; `rcp` = 1.0f / d computed once.  An integer division by a run-time value costs ~25 instructions.
+// (float)n is exact; rcp and the product carry a relative error of 2^-24 each.
 __device__ __forceinline__ int fast_div(int n, int d, float rcp) {
   int q = (int)((float)n * rcp);
-  const int r = n - q * d;
-  q += (r >= d) ? 1 : 0;
-  q -= (r < 0) ? 1 : 0;
+  int r = n - q * d;
+  // the estimate is off by less than (n / d) 2^-22 + 1: one step for quotients below 2^22 (every use but a
+  // single-anchor map of more than 4M cells), at most three in general
+  while (r >= d) {
+    ++q;
+    r -= d;
+  }
+  while (r < 0) {
+    --q;
+    r += d;
+  }
   return q;
 }
 
