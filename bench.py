@@ -508,7 +508,7 @@ def run_gpu_arm(args, rank, world, local_rank):
             ach = bytes_launch / per_launch_s / 1e9
             # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel at this
             # configuration (profiles/r01h_cluster_kernel_ncu.md); not re-measured here (never time under a profiler)
-            traffic = 3564032 if (dom == "proposal_cluster_kernel" and B == 8 and CONFIG == "voc_test") else None
+            traffic = 3893248 if (dom == "proposal_cluster_kernel" and B == 8 and CONFIG == "voc_test") else None
             roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                     "us_per_launch": d["us_per_launch"], "share_of_step": d["share"]}
