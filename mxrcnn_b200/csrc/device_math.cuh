@@ -149,18 +149,10 @@ __device__ __forceinline__ double clip_0_lim(double v, double lim) {
 // (h, w, a) index the cropped map; deltas are read from the full (4A,H,W) map of the image.
 // f64 arithmetic, exp in f32 (numpy evaluates np.exp on the f32 deltas), clip limits are
 // the f32 scalars im_info[k]-1.
-__device__ __forceinline__ void decode_clip(const AnchorTable& at, const DecodeGeom& g, const float* __restrict__ deltas,
-                                            int h, int w, int a, float im_h, float im_w, double out[4],
-                                            bool* delta_nan = nullptr) {
+// The arithmetic, for deltas (dx, dy, dw, dh) already in registers.
+__device__ __forceinline__ void decode_clip_values(const AnchorTable& at, const DecodeGeom& g, float dx, float dy, float dw,
+                                                   float dh, int h, int w, int a, float im_h, float im_w, double out[4]) {
   typedef Ar<double> A;
-  const size_t hw = (size_t)g.H * g.W;
-  const size_t base = ((size_t)a * 4) * hw + (size_t)h * g.W + w;
-  const float dx = __ldg(deltas + base);
-  const float dy = __ldg(deltas + base + hw);
-  const float dw = __ldg(deltas + base + 2 * hw);
-  const float dh = __ldg(deltas + base + 3 * hw);
-  // fmin/fmax in the clip below drop NaNs, so the reference's NaN check (proposal.py:61) looks at the raw deltas
-  if (delta_nan) *delta_nan = (dx != dx) || (dy != dy) || (dw != dw) || (dh != dh);
   const double sx = A::mul((double)w, g.fs);
   const double sy = A::mul((double)h, g.fs);
   const double ax1 = A::add(at.a[a][0], sx), ay1 = A::add(at.a[a][1], sy);
@@ -181,6 +173,21 @@ __device__ __forceinline__ void decode_clip(const AnchorTable& at, const DecodeG
   out[1] = clip_0_lim(A::sub(pcy, hy), lim_y);
   out[2] = clip_0_lim(A::add(pcx, hx), lim_x);
   out[3] = clip_0_lim(A::add(pcy, hy), lim_y);
+}
+
+// Loads + arithmetic for one anchor.
+__device__ __forceinline__ void decode_clip(const AnchorTable& at, const DecodeGeom& g, const float* __restrict__ deltas,
+                                            int h, int w, int a, float im_h, float im_w, double out[4],
+                                            bool* delta_nan = nullptr) {
+  const size_t hw = (size_t)g.H * g.W;
+  const size_t base = ((size_t)a * 4) * hw + (size_t)h * g.W + w;
+  const float dx = __ldg(deltas + base);
+  const float dy = __ldg(deltas + base + hw);
+  const float dw = __ldg(deltas + base + 2 * hw);
+  const float dh = __ldg(deltas + base + 3 * hw);
+  // the clip drops NaNs, so the reference's NaN check (proposal.py:61) looks at the raw deltas
+  if (delta_nan) *delta_nan = (dx != dx) || (dy != dy) || (dw != dw) || (dh != dh);
+  decode_clip_values(at, g, dx, dy, dw, dh, h, w, a, im_h, im_w, out);
 }
 
 // proposal.py:156-161 with min_size*im_info[2] evaluated in f32 (NEP 50) and promoted.

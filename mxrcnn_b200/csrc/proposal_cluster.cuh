@@ -137,33 +137,57 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   u32 rk[ITEMS];
   {
     int nvalid = 0, nnan = 0;
+    // Groups of four anchors per thread: first ALL the loads of the group (five floats per anchor, independent of each
+    // other), then the arithmetic -- otherwise the compiler walks the anchors one at a time and a thread pays one DRAM
+    // round trip per anchor.
+    constexpr int kGroup = ITEMS < 4 ? ITEMS : 4;
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const int q = q_begin + tid + i * 1024;
-      u32 key = 0;
-      bool nan = false;
-      if (q < q_end) {
-        const int a = fast_div(q, hwc, rcp_hwc), r = q - a * hwc;
-        const int h = fast_div(r, dg.wc, rcp_wc), w = r - h * dg.wc;
-        double bx[4];
-        bool dnan;
-        decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx, &dnan);
-        float s;
-        if (!pg.cropped) {
-          s = __ldg(fg + (size_t)a * hw + (size_t)h * dg.W + w);
-        } else {  // quirk Q1: scores are read at the flat (H,W,A) index of the UNCROPPED map
-          const int p = r * dg.A + a;
-          const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
-          s = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
+    for (int i0 = 0; i0 < ITEMS; i0 += kGroup) {
+      int ia[kGroup], ih[kGroup], iw[kGroup];
+      float dx[kGroup], dy[kGroup], dw[kGroup], dh[kGroup], sc[kGroup];
+#pragma unroll
+      for (int j = 0; j < kGroup; ++j) {
+        const int q = q_begin + tid + (i0 + j) * 1024;
+        ia[j] = -1;
+        ih[j] = iw[j] = 0;
+        dx[j] = dy[j] = dw[j] = dh[j] = sc[j] = 0.0f;
+        if (q < q_end) {
+          const int a = fast_div(q, hwc, rcp_hwc), r = q - a * hwc;
+          const int h = fast_div(r, dg.wc, rcp_wc), w = r - h * dg.wc;
+          ia[j] = a;
+          ih[j] = h;
+          iw[j] = w;
+          const float* d = deltas + ((size_t)a * 4) * hw + (size_t)h * dg.W + w;
+          dx[j] = __ldg(d);
+          dy[j] = __ldg(d + hw);
+          dw[j] = __ldg(d + 2 * hw);
+          dh[j] = __ldg(d + 3 * hw);
+          if (!pg.cropped) {
+            sc[j] = __ldg(fg + (size_t)a * hw + (size_t)h * dg.W + w);
+          } else {  // quirk Q1: scores are read at the flat (H,W,A) index of the UNCROPPED map
+            const int p = r * dg.A + a;
+            const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
+            sc[j] = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
+          }
         }
-        const bool valid = passes_min_size(bx, g.min_size, im_s);
-        nan = (s != s) || dnan;
-        key = valid ? score_key32(s) : 0u;
       }
-      rk[i] = key;
-      if (key != 0u) atomicAdd(&s_bins[head_bin_of_key(key)], 1u);  // head selection table, see cluster_bin_select
-      nvalid += __popc(__ballot_sync(0xffffffffu, key != 0u));
-      nnan += __popc(__ballot_sync(0xffffffffu, nan));
+#pragma unroll
+      for (int j = 0; j < kGroup; ++j) {
+        u32 key = 0;
+        bool nan = false;
+        if (ia[j] >= 0) {
+          double bx[4];
+          decode_clip_values(g.at, dg, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], im_h, im_w, bx);
+          const bool valid = passes_min_size(bx, g.min_size, im_s);
+          // the clip drops NaNs, so the reference's NaN check (proposal.py:58-62) looks at the raw values
+          nan = (sc[j] != sc[j]) || (dx[j] != dx[j]) || (dy[j] != dy[j]) || (dw[j] != dw[j]) || (dh[j] != dh[j]);
+          key = valid ? score_key32(sc[j]) : 0u;
+        }
+        rk[i0 + j] = key;
+        if (key != 0u) atomicAdd(&s_bins[head_bin_of_key(key)], 1u);  // head selection table, see cluster_bin_select
+        nvalid += __popc(__ballot_sync(0xffffffffu, key != 0u));
+        nnan += __popc(__ballot_sync(0xffffffffu, nan));
+      }
     }
     if (pg.cropped) {  // proposal.py:58-62 checks the whole arrays, cropped or not
       const int fchunk = (pg.n_full + csize - 1) / csize;
