@@ -26,35 +26,8 @@ __device__ __forceinline__ float4 ldcg_box<float>(const float4* p) {
   return __ldcg(p);
 }
 
-// Descending bitonic sort of n_pow2 <= 1024 distinct 64-bit keys, one key per thread (blockDim.x == 1024):
-// strides below 32 are warp shuffles, only strides >= 32 go through shared memory (15 of the 55 stages).
-__device__ __forceinline__ void bitonic_sort_1024_regs(u64* buf, int n_pow2) {
-  const int t = threadIdx.x;
-  u64 v = buf[t];  // entries beyond the real keys are zero-padded by the caller up to 1024
-  for (int size = 2; size <= n_pow2; size <<= 1) {
-    const bool desc = (t & size) == 0;
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      u64 other;
-      if (stride < 32) {
-        other = __shfl_xor_sync(0xffffffffu, v, stride);
-      } else {
-        __syncthreads();
-        buf[t] = v;
-        __syncthreads();
-        other = buf[t ^ stride];
-      }
-      const bool lower = (t & stride) == 0;
-      const bool take_max = (lower == desc);
-      const bool other_gt = other > v;
-      v = (take_max == other_gt) ? other : v;
-    }
-  }
-  __syncthreads();
-  buf[t] = v;
-  __syncthreads();
-}
-
-// Same sort with FOUR keys per thread on the first 256 threads (blockDim.x == 1024, all threads call it; the other
+// Descending bitonic sort of n_pow2 <= 1024 distinct 64-bit keys (entries beyond the real keys are zero-padded by the
+// caller up to 1024), FOUR keys per thread on the first 256 threads (blockDim.x == 1024, all threads call it; the other
 // 768 only wait at the end): strides 1-2 are register compare-exchanges, 4..64 warp shuffles, and only strides
 // >= 128 -- 6 of the 55 stages -- go through shared memory, synchronised by a 256-thread named barrier
 // instead of a block-wide one.
@@ -227,9 +200,6 @@ struct StripeWalker {
   u64* L_removed;
   typename Ar<T>::Box* t_box;       // this warp's staging: [16]
   T* t_area;
-  u64* s_keptbits;
-  int* s_finish;
-  int* s_local;                     // [4] scratch of this CTA
   T thr;
   int max_keep;
   // walk state (identical in every thread of the cluster)

@@ -42,8 +42,6 @@ __global__ void __launch_bounds__(1024, 1) nms_cluster_kernel(NmsClusterArgs<T> 
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ __align__(8) int s_status[2];
   __shared__ int s_local[4];
-  __shared__ u64 s_keptbits;
-  __shared__ int s_finish;
   cgx::cluster_group cluster = cgx::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int csize = (int)cluster.num_blocks();
@@ -121,9 +119,6 @@ __global__ void __launch_bounds__(1024, 1) nms_cluster_kernel(NmsClusterArgs<T> 
   wk.L_removed = cluster.map_shared_rank(s_removed, 0);
   wk.t_box = t_box;
   wk.t_area = t_area;
-  wk.s_keptbits = &s_keptbits;
-  wk.s_finish = &s_finish;
-  wk.s_local = s_local;
   wk.thr = g.thr;
   wk.max_keep = g.max_keep;
   wk.nk = 0;

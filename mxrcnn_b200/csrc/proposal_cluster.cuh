@@ -88,8 +88,6 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   __shared__ u32 s_st[4];
   __shared__ int s_local[4];
   __shared__ int s_pub[2];  // this CTA's valid / NaN counts of the decode phase, read by the other CTAs
-  __shared__ u64 s_keptbits;
-  __shared__ int s_finish;
   cgx::cluster_group cluster = cgx::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int csize = (int)cluster.num_blocks();
@@ -530,9 +528,6 @@ __global__ void __launch_bounds__(1024, 1) proposal_cluster_kernel(ClusterArgs g
   wk.L_removed = L_removed;
   wk.t_box = t_box;
   wk.t_area = t_area;
-  wk.s_keptbits = &s_keptbits;
-  wk.s_finish = &s_finish;
-  wk.s_local = s_local;
   wk.thr = g.thr;
   wk.max_keep = g.max_keep;
   wk.nk = 0;
