@@ -95,7 +95,22 @@ def main():
     rows.append({"workload": "nms 0.3, 2000 dets f64 (configs[4] test-time NMS), host arrays",
                  "gpu_us_per_call": wall(lambda: nms(d2000, 0.3), 20) * 1e6,
                  "cpu_1core_ms_per_image": wall(lambda: restate.nms(d2000, 0.3), 3, 1) * 1e3})
+    from mxrcnn_b200.rcnn.tester import detections
+    r, d, sc, shp, scl = synth.box_head_inputs(7)
+    rows.append({"workload": "test-time box head 300 rois x 21 classes (detector.py:73-74 + tester.py:50-65), host arrays",
+                 "gpu_us_per_call": wall(lambda: detections(sc, r, d, shp, scl), 20) * 1e6,
+                 "cpu_1core_ms_per_image": wall(lambda: restate.box_head(r, d, sc, shp, scl), 3, 1) * 1e3})
     print(json.dumps(rows, indent=1))
+    if len(sys.argv) > 1:  # markdown table for profiles/
+        with open(sys.argv[1], "w") as f:
+            f.write("| workload | GPU us / call | GPU images/s | numpy restatement ms / image (1 core) | note |\n|---|---|---|---|---|\n")
+            for x in rows:
+                note = ""
+                if x.get("stripes_walked") is not None:
+                    note = "%.0f stripes of 256 walked; nkeep >= %d" % (x["stripes_walked"], x["nkeep_min"])
+                f.write("| %s | %.1f | %s | %.1f | %s |\n" % (
+                    x["workload"], x["gpu_us_per_call"], ("%.0f" % x["gpu_images_per_s"]) if "gpu_images_per_s" in x else "-",
+                    x["cpu_1core_ms_per_image"], note))
 
 
 if __name__ == "__main__":
