@@ -66,6 +66,9 @@ SIGNATURES = {
     "mxr_last_launch_count": (ctypes.c_int, [_VP]),
     "mxr_bench_alu_peak": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p]),
     "mxr_proposal_phase_times": (ctypes.c_int, [_VP, ctypes.c_int, c_double_p, c_int_p]),
+    "mxr_proposal_stamps": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64), c_int_p]),
+    "mxr_proposal_count_pairs": (ctypes.c_int, [_VP, ctypes.c_int]),
+    "mxr_proposal_pairs_read": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), c_int_p]),
     "mxr_generate_anchors": (ctypes.c_int, [ctypes.c_double, c_double_p, ctypes.c_int, c_double_p, ctypes.c_int,
                                             c_double_p]),
     "mxr_reserve_proposal": (ctypes.c_int, [_VP, ctypes.POINTER(ProposalParams)]),
@@ -187,6 +190,25 @@ class Handle(object):
             d["stripes_walked"] = int(us[b * 9 + 8])
             out.append(d)
         return out
+
+    def proposal_stamps(self, max_images=64):
+        """Raw %globaltimer stamps (ns) and counters of the last fused proposal launch: (images, 16) uint64."""
+        buf = np.zeros((max_images, 16), np.uint64)
+        n = ctypes.c_int32(0)
+        check(load().mxr_proposal_stamps(self._h, max_images, buf.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
+                                         ctypes.byref(n)))
+        return buf[:n.value]
+
+    def count_pairs(self, on):
+        check(load().mxr_proposal_count_pairs(self._h, 1 if on else 0))
+
+    def pairs_read(self, max_images=1024):
+        """IoU pairs evaluated per image by the last fused proposal call made while count_pairs(True) was set."""
+        buf = np.zeros((max_images,), np.uint32)
+        n = ctypes.c_int32(0)
+        check(load().mxr_proposal_pairs_read(self._h, max_images, buf.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
+                                             ctypes.byref(n)))
+        return buf[:n.value]
 
     def last_launch_count(self):
         return int(load().mxr_last_launch_count(self._h))

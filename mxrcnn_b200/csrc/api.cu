@@ -54,9 +54,9 @@ int ensure_pinned_ws(Handle* h, size_t bytes) {
 // Kernel attributes and the occupancy figures derived from them, per device, shared by all handles.
 static const int kMaxDevices = 64;
 struct DeviceCache {
-  int smem_attr[8];
+  int smem_attr[12];
   int coop_grid[4];
-  int cluster_cap[16];
+  int cluster_cap[32];
 };
 static DeviceCache g_dev_cache[kMaxDevices];
 static std::mutex g_dev_mutex;
@@ -102,6 +102,8 @@ int mxr_create(int device, mxr_handle_t* out) {
   h->cluster_override = (c8 && c8[0] == '1') ? 8 : 0;
   const char* np = getenv("MXRCNN_B200_NO_PDL");
   h->no_pdl = (np && np[0] == '1') ? 1 : 0;
+  const char* v1 = getenv("MXRCNN_B200_V1");
+  h->use_v1 = (v1 && v1[0] == '1') ? 1 : 0;
   const char* cs = getenv("MXRCNN_B200_CLUSTER");
   if (cs) {
     const int v = atoi(cs);
@@ -206,6 +208,40 @@ int mxr_proposal_phase_times(mxr_handle_t hh, int max_images, double* us_out, in
     us_out[b * 9 + 8] = (double)tmp[b * 16 + 9];
   }
   delete[] tmp;
+  *images_out = n;
+  return MXR_OK;
+}
+
+int mxr_proposal_stamps(mxr_handle_t hh, int max_images, uint64_t* ns_out, int32_t* images_out) {
+  MXR_REQUIRE(hh != nullptr && ns_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
+              "mxr_proposal_stamps: bad argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  *images_out = 0;
+  if (!h->dbg_ptr || h->dbg_images <= 0) return MXR_OK;
+  MXR_CUDA(cudaDeviceSynchronize());
+  const int n = h->dbg_images < max_images ? h->dbg_images : max_images;
+  MXR_CUDA(cudaMemcpy(ns_out, h->dbg_ptr, (size_t)n * 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  *images_out = n;
+  return MXR_OK;
+}
+
+int mxr_proposal_count_pairs(mxr_handle_t hh, int on) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_count_pairs: NULL handle");
+  reinterpret_cast<Handle*>(hh)->count_pairs = on ? 1 : 0;
+  return MXR_OK;
+}
+
+int mxr_proposal_pairs_read(mxr_handle_t hh, int max_images, uint32_t* pairs_out, int32_t* images_out) {
+  MXR_REQUIRE(hh != nullptr && pairs_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
+              "mxr_proposal_pairs_read: bad argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  *images_out = 0;
+  if (!h->pair_ptr || h->pair_images <= 0) return MXR_OK;
+  MXR_CUDA(cudaDeviceSynchronize());
+  const int n = h->pair_images < max_images ? h->pair_images : max_images;
+  MXR_CUDA(cudaMemcpy(pairs_out, h->pair_ptr, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
   *images_out = n;
   return MXR_OK;
 }

@@ -93,16 +93,21 @@ struct Handle {
   int last_launches;  // kernels launched by the most recent call
   // Both point into the process-wide table of this handle's DEVICE (api.cu): kernel attributes belong to
   // (kernel, device), not to a handle, so two handles must not cache them separately.
-  int* smem_attr;     // [8] largest dynamic-smem opt-in already set per kernel (1 prep f32, 2 prep f64, 3 coop,
-                      // 4/5 fused proposal, 6/7 cluster NMS); raise it through raise_dyn_smem() only
+  int* smem_attr;     // [12] largest dynamic-smem opt-in already set per kernel (1 prep f32, 2 prep f64, 3 coop,
+                      // 4/5 first-generation fused proposal, 6/7 cluster NMS, 8/9 fused proposal); raise it through
+                      // raise_dyn_smem() only
   int* coop_grid;     // [4] [0] co-resident grid of the cooperative NMS kernel (0: not queried)
-  int* cluster_cap;   // [2][8] fused proposal kernel (4 / 12 keys per thread) x cluster size (16, 14, ... 2): clusters
-                      // resident at once; 0 not queried, -1 none
+  int* cluster_cap;   // [4][8] fused proposal kernels (first generation 4 / 12 keys per thread, second generation 4 / 12)
+                      // x cluster size (16, 14, ... 2): clusters resident at once; 0 not queried, -1 none
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
   int cluster_override; // MXRCNN_B200_CLUSTER=2|4|8|16 pins the cluster size of the fused proposal kernel (tests cover
                         // them all); MXRCNN_B200_CLUSTER8=1 is the older spelling of 8.  0: chosen per call
   int no_pdl;           // MXRCNN_B200_NO_PDL=1: launch the fused kernel without programmatic dependent launch
+  int use_v1;           // MXRCNN_B200_V1=1: first-generation fused kernel (proposal_cluster.cuh) instead of proposal_fused.cuh
+  int count_pairs;      // mxr_proposal_count_pairs(h, 1): the next fused calls count the IoU pairs they evaluate (un-timed runs)
+  unsigned int* pair_ptr;  // device: per-image pair counters of the last such call
+  int pair_images;
   unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
   int dbg_images;
   cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path

@@ -1,10 +1,12 @@
 // rcnn/rpn/proposal.py:39-149 -- host side of the proposal operator.
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include "nms_coop.cuh"
 #include "nms_host.cuh"
 #include "proposal_cluster.cuh"
+#include "proposal_fused.cuh"
 #include "proposal_kernels.cuh"
 
 using namespace mxr;
@@ -31,6 +33,13 @@ struct Layout {
   u64* M;
   u64* g_sort_keys;
   u64* dbg;  // [B][16] phase time stamps of the fused kernel
+  // second-generation fused kernel (proposal_fused.cuh)
+  u64* comp;      // [B][n_crop] bucketed composites
+  float4* kbox;   // [B][keep_cap]
+  float4* kaux;   // [B][keep_cap]
+  u64* fsort;     // [B][fsort_cap] scratch for crowded buckets
+  int fsort_cap;
+  u32* pair_count;  // [B]
   // staging for the *_host entry point
   float* d_cls;
   float* d_box;
@@ -86,6 +95,12 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   L->M = c.take<u64>((size_t)L->B * m_words);
   L->g_sort_keys = L->use_smem_sort ? nullptr : c.take<u64>((size_t)L->B * L->n_pow2_max);
   L->dbg = c.take<u64>((size_t)L->B * 16);
+  L->comp = c.take<u64>((size_t)L->B * L->n_crop);
+  L->kbox = c.take<float4>((size_t)L->B * L->keep_cap);
+  L->kaux = c.take<float4>((size_t)L->B * L->keep_cap);
+  L->fsort_cap = pow2_ceil(L->n_crop < 2 ? 2 : L->n_crop);
+  L->fsort = c.take<u64>((size_t)L->B * L->fsort_cap);
+  L->pair_count = c.take<u32>((size_t)L->B);
   if (host_io) {
     const size_t hw = (size_t)L->H * L->W;
     L->d_cls = c.take<float>((size_t)L->B * L->A * hw);  // foreground half only
@@ -120,6 +135,153 @@ struct ProposalTier2 {
   }
 };
 
+
+// Second-generation fused kernel (proposal_fused.cuh): ONE launch, any list length.  Returns MXR_ERR_UNSUPPORTED when an
+// image does not fit 16 CTAs x 12 keys x 1024 threads (the caller then takes the multi-kernel path).
+static const int MXR_ERR_UNSUPPORTED = -1000;
+int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layout& L, const ProposalGeom& pg,
+                  const AnchorTable& at, const float* cls_prob, const float* bbox_pred, const float* im_info, float* out_rois,
+                  float* out_scores, int32_t* out_keep, int32_t* out_anchor, int32_t* out_nkeep) {
+  static const int kNumSizes = 8;
+  static const int kSizes[kNumSizes] = {16, 14, 12, 10, 8, 6, 4, 2};
+  static const double kWaveCost[kNumSizes] = {0.883, 0.89, 0.925, 0.99, 1.0, 1.075, 1.35, 1.85};
+  if ((L.n_crop + 16 * 1024 - 1) / (16 * 1024) > 12) return MXR_ERR_UNSUPPORTED;
+  fz::FusedArgs* fa = new fz::FusedArgs();
+  struct Guard {
+    fz::FusedArgs* p;
+    ~Guard() { delete p; }
+  } guard{fa};
+  memset(fa, 0, sizeof(*fa));
+  fa->pg = pg;
+  fa->at = at;
+  const double fs = p->feat_stride;
+  fa->fs32 = (float)fs;
+  fa->fs_err = (float)fabs(fs - (double)fa->fs32) * 1.0000002f;
+  for (int a = 0; a < L.A; ++a) {
+    // bbox_transform.py:47-50 on the base anchor: width, height, centre (the shift w * feat_stride is added in the kernel)
+    const double bw = at.a[a][2] - at.a[a][0] + 1.0, bh = at.a[a][3] - at.a[a][1] + 1.0;
+    const double cx = at.a[a][0] + 0.5 * (bw - 1.0), cy = at.a[a][1] + 0.5 * (bh - 1.0);
+    const double v[4] = {bw, bh, cx, cy};
+    float f[4];
+    double err = 0.0;
+    for (int k = 0; k < 4; ++k) {
+      f[k] = (float)v[k];
+      const double d = fabs(v[k] - (double)f[k]);
+      if (d > err) err = d;
+    }
+    fa->at32[a] = make_float4(f[0], f[1], f[2], f[3]);
+    // the kernel multiplies deltas (|dx| can be large) into bw / bh: a converted width carries a RELATIVE error, which
+    // the kernel's bound covers through its 2^-23 |dx * bw| term as long as the conversion is within 2^-24 relative (it is)
+    fa->at_err[a] = (float)err * 1.0000002f + (err > 0.0 ? 1e-30f : 0.0f);
+  }
+  fa->cls_prob = cls_prob;
+  fa->bbox_pred = bbox_pred;
+  fa->im_info = im_info;
+  fa->min_size = p->min_size;
+  fa->pre_nms = p->pre_nms_top_n;
+  fa->max_keep = p->post_nms_top_n > 0 ? L.keep_cap : 0;
+  // stripe widths: the first stripe should settle a small quota on its own (the 300th keep sits near sorted position
+  // 390 at the BASELINE configuration); later stripes and quota-less walks use the widest stripe
+  int w0 = fz::kWMax, w1 = fz::kWMax;
+  if (fa->max_keep > 0 && fa->max_keep < 360) {
+    w0 = round_up_int(fa->max_keep + fa->max_keep / 2 + 32, 32);
+    if (w0 > fz::kWMax) w0 = fz::kWMax;
+    w1 = 256;
+  }
+  if (p->first_stripe > 0) {
+    w0 = round_up_int(p->first_stripe, 32);
+    if (w0 > fz::kWMax) w0 = fz::kWMax;
+  }
+  fa->first_stripe = w0;
+  fa->next_stripe = w1;
+  fa->window0 = fa->max_keep > 0 ? 2 * fa->max_keep + 256 : 0;
+  fa->thr = p->nms_thresh;
+  fa->comp = L.comp;
+  fa->kbox = L.kbox;
+  fa->kaux = L.kaux;
+  fa->keep_cap = L.keep_cap;
+  fa->sortbuf = L.fsort;
+  fa->sort_cap = L.fsort_cap;
+  fa->o.rois = out_rois;
+  fa->o.scores = out_scores;
+  fa->o.keep_pos = out_keep;
+  fa->o.keep_orig = out_anchor;
+  fa->o.nkeep = out_nkeep;
+  fa->o.rows = L.out_rows;
+  fa->o.row_offsets = nullptr;
+  fa->ctrl = L.ctrl;
+  fa->dbg = h->prof_on ? L.dbg : nullptr;
+  h->dbg_ptr = fa->dbg;
+  h->dbg_images = fa->dbg ? L.B : 0;
+  fa->pair_count = h->count_pairs ? L.pair_count : nullptr;
+  h->pair_ptr = fa->pair_count;
+  h->pair_images = fa->pair_count ? L.B : 0;
+  if (fa->pair_count) MXR_CUDA(cudaMemsetAsync(L.pair_count, 0, (size_t)L.B * sizeof(u32), s));
+  const size_t smem = fz::fused_smem_bytes();
+  int csize = 0, items = 0;
+  double best = 0;
+  int pinned = h->cluster_override;  // ignored when the image does not fit 12 keys per thread at that size
+  if (pinned && (L.n_crop + pinned * 1024 - 1) / (pinned * 1024) > 12) pinned = 0;
+  for (int c = 0; c < kNumSizes; ++c) {
+    const int cs = kSizes[c];
+    if (pinned && pinned != cs) continue;
+    const int it = (L.n_crop + cs * 1024 - 1) / (cs * 1024);
+    if (it > 12) continue;
+    const int v = it <= 4 ? 0 : 1;
+    void (*kq)(const fz::FusedArgs) = v == 0 ? fz::proposal_fused_kernel<4> : fz::proposal_fused_kernel<12>;
+    MXR_TRY(raise_dyn_smem(h, 8 + v, (const void*)kq, smem, nullptr));
+    int& cap = h->cluster_cap[(2 + v) * kNumSizes + c];
+    if (cap == 0) {
+      cudaLaunchConfig_t q;
+      memset(&q, 0, sizeof(q));
+      q.gridDim = dim3(cs);
+      q.blockDim = dim3(1024);
+      q.dynamicSmemBytes = smem;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = cs;
+      qa[0].val.clusterDim.y = 1;
+      qa[0].val.clusterDim.z = 1;
+      q.attrs = qa;
+      q.numAttrs = 1;
+      int n = 0;
+      if (cs > 8 && cudaFuncSetAttribute(kq, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) n = -1;
+      if (n == 0 && cudaOccupancyMaxActiveClusters(&n, kq, &q) != cudaSuccess) n = -1;
+      (void)cudaGetLastError();
+      cap = n > 0 ? n : -1;
+    }
+    if (cap <= 0) continue;
+    const double cost = (double)((L.B + cap - 1) / cap) * kWaveCost[c];
+    if (csize == 0 || cost < best) {
+      csize = cs;
+      items = it;
+      best = cost;
+    }
+  }
+  MXR_REQUIRE(csize != 0, MXR_ERR_CUDA, "proposal: no cluster size of the fused kernel fits this device");
+  void (*kern)(const fz::FusedArgs) = items <= 4 ? fz::proposal_fused_kernel<4> : fz::proposal_fused_kernel<12>;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(L.B * csize);
+  cfg.blockDim = dim3(1024);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = csize;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (h->no_pdl || fa->pair_count) ? 1 : 2;
+  prof_begin(h, s, ST_CLUSTER);
+  MXR_CUDA(cudaLaunchKernelEx(&cfg, kern, *fa));
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
 int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layout& L, const float* cls_prob,
             size_t cls_img_stride, size_t cls_fg_offset, const float* bbox_pred, const float* im_info,
             const double* anchors, float* out_rois, float* out_scores, int32_t* out_keep, int32_t* out_anchor,
@@ -144,6 +306,11 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   // an image's anchors to fit 8 CTAs x 12 keys x 1024 threads and the pre-NMS list to fit the leader's
   // shared-memory sort buffer; otherwise, or with MXRCNN_B200_NO_CLUSTER=1 (used by the tests to cover both),
   // the multi-kernel path runs.
+  if (!h->no_cluster && !h->use_v1) {
+    const int st = enqueue_fused(h, s, p, L, pg, at, cls_prob, bbox_pred, im_info, out_rois, out_scores, out_keep, out_anchor,
+                                 out_nkeep);
+    if (st != MXR_ERR_UNSUPPORTED) return st;  // an image too large for 16 CTAs x 12 keys x 1024 threads: multi-kernel path
+  }
   const int cluster_items = (L.n_crop + kClusterSize * 1024 - 1) / (kClusterSize * 1024);
   int sort_cap = pow2_ceil(L.n_max > L.head ? L.n_max : L.head);
   if (sort_cap < 1024) sort_cap = 1024;

@@ -241,3 +241,21 @@ def test_head_selection_when_scores_crowd_few_bins(cfgname, lo, width):
     st = restate.proposal_stages(cls, box, info, cfg["feat_stride"], cfg["scales"], cfg["ratios"], False, cfg["pre"],
                                  cfg["post"], cfg["thresh"], cfg["min_size"], nms_stop_after=cfg["post"])
     check_against(st, out, cfg["post"])
+
+
+@pytest.mark.parametrize("cfgname,seed", [("tiny", 91), ("voc_test", 92), ("voc_train", 93), ("voc_alt", 94), ("wider", 95)])
+def test_first_generation_fused_kernel_agrees(cfgname, seed, monkeypatch):
+    """MXRCNN_B200_V1=1 selects the first-generation fused kernel (sorted head, float64 pair tests everywhere);
+    the default kernel (bucketed list, float32 screen in front of the float64 test) must give the same bits."""
+    from mxrcnn_b200 import _lib
+    cfg = synth.CONFIGS[cfgname]
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    new = run(cls, box, info, cfg, rng=np.random.RandomState(seed))
+    monkeypatch.setenv("MXRCNN_B200_V1", "1")
+    h = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_V1")
+    old = run(cls, box, info, cfg, rng=np.random.RandomState(seed), handle=h)
+    for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
+        assert np.array_equal(new[k], old[k]), k
+    h.close()
