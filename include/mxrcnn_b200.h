@@ -73,13 +73,16 @@ int mxr_last_launch_count(mxr_handle_t h);
  * proposal launch: us_out[image*9 + i], i = 0 start-up barrier, 1 decode, 2 select, 3 compact, 4 sort,
  * 5 re-decode, 6 NMS stripes, 7 outputs; [8] = number of 256-box stripes walked.  Synchronises. */
 int mxr_proposal_phase_times(mxr_handle_t h, int max_images, double* us_out, int32_t* images_out);
-/* The raw stamps of the same launch: ns_out[image*16 + i].  i = 0..8 the phase boundaries above; fused kernel of
+/* The raw stamps of the same launch: ns_out[image*48 + i].  i = 0..8 the phase boundaries above; fused kernel of
  * proposal_fused.cuh additionally: 10 first stripe staged, 11 its IoU bit blocks done, 12 barrier passed, 13 stripe
- * resolved by the leader; [9] stripes walked, [14] windows materialised, [15] fixed-point rounds of the first stripe. */
+ * resolved by the leader; [9] stripes walked, [14] windows materialised, [15] fixed-point rounds of the first stripe;
+ * 16..47: SM cycle counter (clock64) of the leader's first thread at fine-grained points of the first stripe
+ * (tools/phase_probe2.py names them). */
 int mxr_proposal_stamps(mxr_handle_t h, int max_images, uint64_t* ns_out, int32_t* images_out);
 /* Instrumented (un-timed) runs for bench.py's ALU roofline: count_pairs(1) makes the following fused proposal calls
  * count the IoU pairs they evaluate (nms.py:25-36 evaluations, SURVEY 8d "pairs_evaluated"); pairs_read() returns the
- * per-image counters of the most recent such call.  Synchronises. */
+ * per-image counters of the most recent such call: pairs_out[2*image] pairs evaluated, [2*image+1] pairs that the
+ * float32 screen could not decide and the float64 arithmetic settled.  Synchronises. */
 int mxr_proposal_count_pairs(mxr_handle_t h, int on);
 int mxr_proposal_pairs_read(mxr_handle_t h, int max_images, uint32_t* pairs_out, int32_t* images_out);
 

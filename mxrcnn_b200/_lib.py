@@ -192,8 +192,8 @@ class Handle(object):
         return out
 
     def proposal_stamps(self, max_images=64):
-        """Raw %globaltimer stamps (ns) and counters of the last fused proposal launch: (images, 16) uint64."""
-        buf = np.zeros((max_images, 16), np.uint64)
+        """Raw %globaltimer stamps (ns), counters and cycle stamps of the last fused proposal launch: (images, 48) uint64."""
+        buf = np.zeros((max_images, 48), np.uint64)
         n = ctypes.c_int32(0)
         check(load().mxr_proposal_stamps(self._h, max_images, buf.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
                                          ctypes.byref(n)))
@@ -203,8 +203,9 @@ class Handle(object):
         check(load().mxr_proposal_count_pairs(self._h, 1 if on else 0))
 
     def pairs_read(self, max_images=1024):
-        """IoU pairs evaluated per image by the last fused proposal call made while count_pairs(True) was set."""
-        buf = np.zeros((max_images,), np.uint32)
+        """(images, 2): IoU pairs evaluated / settled by the float64 test, per image, by the last fused proposal call
+        made while count_pairs(True) was set."""
+        buf = np.zeros((max_images, 2), np.uint32)
         n = ctypes.c_int32(0)
         check(load().mxr_proposal_pairs_read(self._h, max_images, buf.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
                                              ctypes.byref(n)))

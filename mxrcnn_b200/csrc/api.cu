@@ -221,7 +221,19 @@ int mxr_proposal_stamps(mxr_handle_t hh, int max_images, uint64_t* ns_out, int32
   if (!h->dbg_ptr || h->dbg_images <= 0) return MXR_OK;
   MXR_CUDA(cudaDeviceSynchronize());
   const int n = h->dbg_images < max_images ? h->dbg_images : max_images;
-  MXR_CUDA(cudaMemcpy(ns_out, h->dbg_ptr, (size_t)n * 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  // device layout: [images][16] phase stamps, then [images][32] cycle stamps; out: 48 values per image
+  uint64_t* tmp = new uint64_t[(size_t)h->dbg_images * 48];
+  cudaError_t e = cudaMemcpy(tmp, h->dbg_ptr, (size_t)h->dbg_images * 48 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) {
+    delete[] tmp;
+    set_error("mxr_proposal_stamps: %s", cudaGetErrorString(e));
+    return MXR_ERR_CUDA;
+  }
+  for (int b = 0; b < n; ++b) {
+    memcpy(ns_out + (size_t)b * 48, tmp + (size_t)b * 16, 16 * sizeof(uint64_t));
+    memcpy(ns_out + (size_t)b * 48 + 16, tmp + (size_t)h->dbg_images * 16 + (size_t)b * 32, 32 * sizeof(uint64_t));
+  }
+  delete[] tmp;
   *images_out = n;
   return MXR_OK;
 }
@@ -241,7 +253,7 @@ int mxr_proposal_pairs_read(mxr_handle_t hh, int max_images, uint32_t* pairs_out
   if (!h->pair_ptr || h->pair_images <= 0) return MXR_OK;
   MXR_CUDA(cudaDeviceSynchronize());
   const int n = h->pair_images < max_images ? h->pair_images : max_images;
-  MXR_CUDA(cudaMemcpy(pairs_out, h->pair_ptr, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  MXR_CUDA(cudaMemcpy(pairs_out, h->pair_ptr, (size_t)n * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
   *images_out = n;
   return MXR_OK;
 }

@@ -32,7 +32,7 @@ struct Layout {
   int* kept_slot;
   u64* M;
   u64* g_sort_keys;
-  u64* dbg;  // [B][16] phase time stamps of the fused kernel
+  u64* dbg;  // [B][16] phase time stamps of the fused kernel, then [B][32] cycle stamps
   // second-generation fused kernel (proposal_fused.cuh)
   u64* comp;      // [B][n_crop] bucketed composites
   float4* kbox;   // [B][keep_cap]
@@ -94,13 +94,13 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   const size_t m_words = (size_t)L->plan.max_width * (L->plan.max_width / 64);
   L->M = c.take<u64>((size_t)L->B * m_words);
   L->g_sort_keys = L->use_smem_sort ? nullptr : c.take<u64>((size_t)L->B * L->n_pow2_max);
-  L->dbg = c.take<u64>((size_t)L->B * 16);
+  L->dbg = c.take<u64>((size_t)L->B * 48);  // 16 phase stamps + 32 cycle stamps (second-generation kernel)
   L->comp = c.take<u64>((size_t)L->B * L->n_crop);
   L->kbox = c.take<float4>((size_t)L->B * L->keep_cap);
   L->kaux = c.take<float4>((size_t)L->B * L->keep_cap);
   L->fsort_cap = pow2_ceil(L->n_crop < 2 ? 2 : L->n_crop);
   L->fsort = c.take<u64>((size_t)L->B * L->fsort_cap);
-  L->pair_count = c.take<u32>((size_t)L->B);
+  L->pair_count = c.take<u32>((size_t)L->B * 2);
   if (host_io) {
     const size_t hw = (size_t)L->H * L->W;
     L->d_cls = c.take<float>((size_t)L->B * L->A * hw);  // foreground half only
@@ -211,32 +211,34 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
   fa->o.row_offsets = nullptr;
   fa->ctrl = L.ctrl;
   fa->dbg = h->prof_on ? L.dbg : nullptr;
+  fa->clk = h->prof_on ? L.dbg + (size_t)L.B * 16 : nullptr;
   h->dbg_ptr = fa->dbg;
   h->dbg_images = fa->dbg ? L.B : 0;
   fa->pair_count = h->count_pairs ? L.pair_count : nullptr;
   h->pair_ptr = fa->pair_count;
   h->pair_images = fa->pair_count ? L.B : 0;
-  if (fa->pair_count) MXR_CUDA(cudaMemsetAsync(L.pair_count, 0, (size_t)L.B * sizeof(u32), s));
-  const size_t smem = fz::fused_smem_bytes();
+  if (fa->pair_count) MXR_CUDA(cudaMemsetAsync(L.pair_count, 0, (size_t)L.B * 2 * sizeof(u32), s));
   int csize = 0, items = 0;
   double best = 0;
   int pinned = h->cluster_override;  // ignored when the image does not fit 12 keys per thread at that size
   if (pinned && (L.n_crop + pinned * 1024 - 1) / (pinned * 1024) > 12) pinned = 0;
+  void (*kq)(const fz::FusedArgs) = fz::proposal_fused_kernel;
   for (int c = 0; c < kNumSizes; ++c) {
     const int cs = kSizes[c];
     if (pinned && pinned != cs) continue;
     const int it = (L.n_crop + cs * 1024 - 1) / (cs * 1024);
     if (it > 12) continue;
+    // the occupancy figure depends on the shared-memory size, which depends on the keys per thread: two buckets
     const int v = it <= 4 ? 0 : 1;
-    void (*kq)(const fz::FusedArgs) = v == 0 ? fz::proposal_fused_kernel<4> : fz::proposal_fused_kernel<12>;
-    MXR_TRY(raise_dyn_smem(h, 8 + v, (const void*)kq, smem, nullptr));
+    const size_t smem_v = fz::fused_smem_bytes(v == 0 ? 4 : 12);
+    MXR_TRY(raise_dyn_smem(h, 8, (const void*)kq, fz::fused_smem_bytes(12), nullptr));
     int& cap = h->cluster_cap[(2 + v) * kNumSizes + c];
     if (cap == 0) {
       cudaLaunchConfig_t q;
       memset(&q, 0, sizeof(q));
       q.gridDim = dim3(cs);
       q.blockDim = dim3(1024);
-      q.dynamicSmemBytes = smem;
+      q.dynamicSmemBytes = smem_v;
       cudaLaunchAttribute qa[1];
       qa[0].id = cudaLaunchAttributeClusterDimension;
       qa[0].val.clusterDim.x = cs;
@@ -259,12 +261,13 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
     }
   }
   MXR_REQUIRE(csize != 0, MXR_ERR_CUDA, "proposal: no cluster size of the fused kernel fits this device");
-  void (*kern)(const fz::FusedArgs) = items <= 4 ? fz::proposal_fused_kernel<4> : fz::proposal_fused_kernel<12>;
+  void (*kern)(const fz::FusedArgs) = fz::proposal_fused_kernel;
+  fa->items = items;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(L.B * csize);
   cfg.blockDim = dim3(1024);
-  cfg.dynamicSmemBytes = smem;
+  cfg.dynamicSmemBytes = fz::fused_smem_bytes(items <= 4 ? 4 : 12);
   cfg.stream = s;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;

@@ -42,6 +42,7 @@ struct FusedArgs {
   float min_size;
   int pre_nms;
   int max_keep;      // > 0: post_nms_top_n
+  int items;         // score keys per thread: ceil(n_crop / (cluster size * 1024))
   int first_stripe;  // width of the first stripe (multiple of 32, <= kWMax)
   int next_stripe;   // width of the later stripes
   int window0;       // candidates the first window should hold
@@ -55,7 +56,8 @@ struct FusedArgs {
   NmsOutputs o;
   Ctrl* ctrl;
   u64* dbg;          // optional [b][16] globaltimer stamps (leader CTA), or null
-  u32* pair_count;   // optional [b] IoU pairs evaluated (instrumented runs only), or null
+  u64* clk;          // optional [b][32] clock64 stamps of the leader's first thread (first stripe), or null
+  u32* pair_count;   // optional [b][2] IoU pairs evaluated / sent to the float64 test (instrumented runs only), or null
 };
 
 __device__ __forceinline__ u64 global_ns() {
@@ -66,6 +68,11 @@ __device__ __forceinline__ u64 global_ns() {
 #define FZ_STAMP(i)                                                               \
   do {                                                                            \
     if (g.dbg && rank == 0 && tid == 0) g.dbg[(size_t)b * 16 + (i)] = global_ns(); \
+  } while (0)
+
+#define FZ_CLK(i)                                                                             \
+  do {                                                                                        \
+    if (g.clk && rank == 0 && tid == 0 && stripes == 0) g.clk[(size_t)b * 32 + (i)] = (u64)clock64(); \
   } while (0)
 
 __device__ __forceinline__ int bin_of_key(u32 key) {
@@ -85,8 +92,11 @@ struct Box32 {
 //   t1 = dx * bw, pcx = t1 + cx, pw = exp(dw) * bw, x1 = pcx - 0.5 * (pw - 1): each operation is within 2^-24 relative,
 //   so |x1 - X1| <= u (|t1| + 2 |pcx| + 1.5 pw + 1) (+ the conversion errors of the anchor and the shift); twice that
 //   is used.  The clip is 1-Lipschitz and its limits are the same float32 scalars in both computations.
-__device__ __forceinline__ Box32 decode32(const FusedArgs& g, float dx, float dy, float dw, float dh, int h, int w, int a,
-                                          float lim_x, float lim_y, float c32) {
+struct Dec32 {
+  float x1, y1, x2, y2, e;
+};
+__device__ __forceinline__ Dec32 decode32_core(const FusedArgs& g, float dx, float dy, float dw, float dh, int h, int w, int a,
+                                               float lim_x, float lim_y) {
   const float u2 = 1.1920929e-07f;  // 2^-23
   const float4 an = g.at32[a];
   const float sx = (float)w * g.fs32, sy = (float)h * g.fs32;
@@ -95,22 +105,30 @@ __device__ __forceinline__ Box32 decode32(const FusedArgs& g, float dx, float dy
   const float pcx = t1 + cx, pcy = t2 + cy;
   const float pw = expf(dw) * an.x, ph = expf(dh) * an.y;
   const float hx = 0.5f * (pw - 1.0f), hy = 0.5f * (ph - 1.0f);
-  float x1 = pcx - hx, y1 = pcy - hy, x2 = pcx + hx, y2 = pcy + hy;
-  x1 = fmaxf(fminf(x1, lim_x), 0.0f);  // same order as clip_0_lim: min with the limit first
-  y1 = fmaxf(fminf(y1, lim_y), 0.0f);
-  x2 = fmaxf(fminf(x2, lim_x), 0.0f);
-  y2 = fmaxf(fminf(y2, lim_y), 0.0f);
+  Dec32 r;
+  r.x1 = fmaxf(fminf(pcx - hx, lim_x), 0.0f);  // same order as clip_0_lim: min with the limit first
+  r.y1 = fmaxf(fminf(pcy - hy, lim_y), 0.0f);
+  r.x2 = fmaxf(fminf(pcx + hx, lim_x), 0.0f);
+  r.y2 = fmaxf(fminf(pcy + hy, lim_y), 0.0f);
   const float conv = g.at_err[a] + (float)(w > h ? w : h) * g.fs_err;
-  const float ex = u2 * (fabsf(t1) + 3.0f * fabsf(pcx) + 2.0f * pw + fabsf(sx) + 2.0f) + conv;
-  const float ey = u2 * (fabsf(t2) + 3.0f * fabsf(pcy) + 2.0f * ph + fabsf(sy) + 2.0f) + conv;
+  const float mx = fabsf(t1) + 3.0f * fabsf(pcx) + 2.0f * pw + sx;
+  const float my = fabsf(t2) + 3.0f * fabsf(pcy) + 2.0f * ph + sy;
+  r.e = __fmaf_rn(u2, fmaxf(mx, my) + 2.0f, conv);
+  return r;
+}
+
+__device__ __forceinline__ Box32 decode32(const FusedArgs& g, float dx, float dy, float dw, float dh, int h, int w, int a,
+                                          float lim_x, float lim_y, float c32) {
+  const float u2 = 1.1920929e-07f;
+  const Dec32 d = decode32_core(g, dx, dy, dw, dh, h, w, a, lim_x, lim_y);
   const float L = fmaxf(lim_x, lim_y);
-  const float e = fmaxf(ex, ey) + u2 * (L + 2.0f);
+  const float e = d.e + u2 * (L + 2.0f);
   Box32 r;
-  r.x1 = x1;
-  r.y1 = y1;
-  r.x2p = x2 + 1.0f;
-  r.y2p = y2 + 1.0f;
-  const float bw = r.x2p - x1, bh = r.y2p - y1;
+  r.x1 = d.x1;
+  r.y1 = d.y1;
+  r.x2p = d.x2 + 1.0f;
+  r.y2p = d.y2 + 1.0f;
+  const float bw = r.x2p - d.x1, bh = r.y2p - d.y1;
   const float area = bw * bh;
   r.a = c32 * area;
   // |D^ - D| for a pair is at most t_i + t_j (derivation: DESIGN.md section 3, "float32 screen"); doubled again here
@@ -120,37 +138,95 @@ __device__ __forceinline__ Box32 decode32(const FusedArgs& g, float dx, float dy
   return r;
 }
 
-// float32 screen of nms.py:25-36 for one pair.  inter > thr * union  <=>  inter > c (area_i + area_j) with
-// c = thr / (1 + thr); the areas arrive scaled by c.  bit 0: suppressed for certain, bit 1: undecided.
-__device__ __forceinline__ void pair32(const Box32& r, const float4 cb, const float2 ca, int j, u32& supp, u32& und) {
+// proposal.py:113-120 for one anchor in the reference's float64 arithmetic (the float32 screen could not decide).
+__device__ __noinline__ bool exact_min_size(const FusedArgs& g, float dx, float dy, float dw, float dh, int h, int w, int a,
+                                            float im_h, float im_w, float im_s) {
+  double bx[4];
+  decode_clip_values(g.at, g.pg.g, dx, dy, dw, dh, h, w, a, im_h, im_w, bx);
+  return passes_min_size(bx, g.min_size, im_s);
+}
+
+// float32 screen of nms.py:25-36 for one row box against up to 32 staged columns.
+// inter > thr * union  <=>  inter > c (area_i + area_j) with c = thr / (1 + thr); the areas arrive scaled by c.
+// supp: bit j set when column j is suppressed for certain; und: bit j set when the pair is inside the error bound
+// (also when d is NaN or a tolerance infinite) and must be decided by the float64 test.
+__device__ __forceinline__ float pair_d(const Box32& r, const float4 cb, const float2 ca, float* tol) {
   const float xx1 = fmaxf(r.x1, cb.x), yy1 = fmaxf(r.y1, cb.y);
   const float xx2 = fminf(r.x2p, cb.z), yy2 = fminf(r.y2p, cb.w);
   const float w = fmaxf(xx2 - xx1, 0.0f), h = fmaxf(yy2 - yy1, 0.0f);
-  const float d = w * h - (r.a + ca.x);
-  const float tol = r.t + ca.y;
-  supp |= (d > tol ? 1u : 0u) << j;
-  und |= (fabsf(d) > tol ? 0u : 1u) << j;  // also taken when d is NaN or the tolerance infinite
+  *tol = r.t + ca.y;
+  return __fmaf_rn(w, h, -(r.a + ca.x));  // a screen, not the reference's arithmetic: contraction is welcome
+}
+__device__ __forceinline__ void block_bits(const Box32& r, const float4* __restrict__ cb, const float2* __restrict__ ca, int jn,
+                                           u32& supp_out, u32& und_out) {
+  u32 supp = 0;
+  bool any_und = false;
+#pragma unroll 4
+  for (int j = 0; j < jn; ++j) {
+    float tol;
+    const float d = pair_d(r, cb[j], ca[j], &tol);
+    supp |= (d > tol ? 1u : 0u) << j;
+    any_und = any_und || !(fabsf(d) > tol);
+  }
+  u32 und = 0;
+  if (any_und) {  // rare: find which
+    for (int j = 0; j < jn; ++j) {
+      float tol;
+      const float d = pair_d(r, cb[j], ca[j], &tol);
+      und |= (fabsf(d) > tol ? 0u : 1u) << j;
+    }
+  }
+  supp_out = supp;
+  und_out = und;
+}
+
+// bbox_pred + clip_boxes for one row index in the reference's float64 arithmetic (proposal.py:110-113).
+__device__ __noinline__ void exact_box(const FusedArgs& g, const float* __restrict__ deltas, float im_h, float im_w, int p,
+                                       double out[4]) {
+  const DecodeGeom& dg = g.pg.g;
+  const int a = p % dg.A, r = p / dg.A, h = r / dg.wc, w = r - h * dg.wc;
+  decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, out);
 }
 
 // The reference's own arithmetic for one pair (float64, nms.py:25-36), both boxes decoded from their row indices.
 __device__ __noinline__ bool exact_pair(const FusedArgs& g, const float* __restrict__ deltas, float im_h, float im_w,
                                         int p_row, int p_col) {
-  const DecodeGeom& dg = g.pg.g;
   double br[4], bc[4];
-  {
-    const int a = p_row % dg.A, r = p_row / dg.A, h = r / dg.wc, w = r - h * dg.wc;
-    decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, br);
-  }
-  {
-    const int a = p_col % dg.A, r = p_col / dg.A, h = r / dg.wc, w = r - h * dg.wc;
-    decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bc);
-  }
+  exact_box(g, deltas, im_h, im_w, p_row, br);
+  exact_box(g, deltas, im_h, im_w, p_col, bc);
   return iou_exceeds<double>(br[0], br[1], br[2], br[3], box_area<double>(br[0], br[1], br[2], br[3]), bc[0], bc[1], bc[2],
                              bc[3], box_area<double>(bc[0], bc[1], bc[2], bc[3]), g.thr);
 }
 
-// grid B * csize CTAs, cluster (csize,1,1), block 1024.  ITEMS: keys per thread (n_crop <= csize * ITEMS * 1024).
-template <int ITEMS>
+// A bucket with more candidates than a stripe is wide (scores crowded into one bin) cannot be ranked by counting while
+// it is staged: the leader CTA orders it in place with a sort in global memory -- first by the selection order (score
+// desc, row desc: proposal.py:123-125 with the documented tie rule) to apply the pre-NMS cut to the first r, then by the
+// processing order (score desc, row asc: nms.py:19 re-sorts the already descending list).  All threads of ONE CTA call it.
+__device__ __noinline__ void presort_bucket(u64* __restrict__ bucket, int m, int r, u64* __restrict__ sb) {
+  const int tid = threadIdx.x;
+  const int n_pow2 = max(2, (int)(1u << (32 - __clz(max(m, 2) - 1))));
+  for (int i = tid; i < n_pow2; i += blockDim.x) sb[i] = i < m ? (__ldcg(bucket + i) ^ 0xffffffffull) : 0ull;
+  __syncthreads();
+  bitonic_sort_desc_u64(sb, n_pow2);
+  for (int i = tid; i < n_pow2; i += blockDim.x) sb[i] = i < r ? (sb[i] ^ 0xffffffffull) : 0ull;
+  __syncthreads();
+  bitonic_sort_desc_u64(sb, n_pow2);
+  for (int i = tid; i < r; i += blockDim.x) bucket[i] = sb[i];
+}
+
+// First bin >= lo_mat whose bucket ends at or before `lim` (s_end is non-increasing in the bin index), kBins if none:
+// two ballots over 32 groups of 32 bins instead of a ten-step dependent binary search.  Whole warps call it.
+__device__ __forceinline__ int first_bin_ending_by(const u32* s_end, int lo_mat, u32 lim, int lane) {
+  const int gb = 32 * lane + 31;
+  const u32 m1 = __ballot_sync(0xffffffffu, gb >= lo_mat && s_end[gb] <= lim);
+  if (!m1) return kBins;
+  const int g1 = __ffs(m1) - 1;
+  const int bin = 32 * g1 + lane;
+  const u32 m2 = __ballot_sync(0xffffffffu, bin >= lo_mat && s_end[bin] <= lim);
+  return 32 * g1 + __ffs(m2) - 1;
+}
+
+// grid B * csize CTAs, cluster (csize,1,1), block 1024.  g.items keys per thread (n_crop <= csize * items * 1024).
 __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_constant__ FusedArgs g) {
   namespace cgx = cooperative_groups;
   extern __shared__ __align__(16) unsigned char dyn_smem[];
@@ -160,12 +236,13 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   __shared__ u32 s_base[kBins];       // cluster-wide: candidates in higher bins = first slot of the bucket
   __shared__ u32 s_cnt[kBins];        // cluster-wide: size of the bucket
   __shared__ u32 s_own[kBins];        // first slot of this CTA's candidates inside the bucket
+  __shared__ u32 s_end[kBins];        // cluster-wide: first slot after the bucket (s_base + s_cnt)
   __shared__ u32 s_ctot[kCoarse], s_csuf[kCoarse];
   __shared__ u32 s_scan[34];
   __shared__ int s_plan[8];           // 0 cut coarse bin, 1 first window's lowest coarse bin, 2 cut bin, 3 r_cut, 4 NaN count
-  __shared__ int s_pub[2];            // this CTA's NaN count (read by the other CTAs)
+  __shared__ int s_pub[2];            // this CTA's NaN flag (read by the other CTAs)
   __shared__ __align__(8) int s_status[2];  // kept so far, quota reached: written by the leader into every CTA
-  __shared__ int s_local[4];
+  __shared__ __align__(16) u32 s_keep[32];  // leader: [2][16] keep words (ping-pong)
   cgx::cluster_group cluster = cgx::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int csize = (int)cluster.num_blocks();
@@ -173,7 +250,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const ProposalGeom& pg = g.pg;
   const DecodeGeom& dg = pg.g;
-  // dynamic shared memory: stripe staging (every CTA) + bit rows and scan state (leader)
+  // dynamic shared memory: stripe staging (every CTA), bit rows (leader), score keys of this CTA's anchors
   float4* s_cbox = reinterpret_cast<float4*>(dyn_smem);                 // [kWMax] x1, y1, x2+1, y2+1
   float2* s_caux = reinterpret_cast<float2*>(s_cbox + kWMax);           // [kWMax] scaled area, tolerance
   u64* s_comp = reinterpret_cast<u64*>(s_caux + kWMax);                 // [kWMax] raw composites of the stripe
@@ -181,22 +258,22 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   int* s_kpos = s_p + kWMax;                                            // [kWMax] position in the pre-NMS order
   u32* s_rem = reinterpret_cast<u32*>(s_kpos + kWMax);                  // [16] this CTA's share of the removed bits
   u32* s_removed = s_rem + 16;                                          // leader: [16] removed by earlier stripes
-  u32* s_keep = s_removed + 16;                                         // leader: [2][16] keep words (ping-pong)
-  u32* s_M = s_keep + 32;                                               // leader: [kWMax][kMPitch] bit rows
+  u32* s_M = s_removed + 16;                                            // leader: [kWMax][kMPitch] bit rows
+  u32* s_keys = s_M + kWMax * kMPitch;                                  // [items (even)][1024] score keys, 0 = filtered out
   u32* L_M = cluster.map_shared_rank(s_M, 0);
   u32* L_removed = cluster.map_shared_rank(s_removed, 0);
+  int stripes = 0;
   if (rank == 0 && tid < 16) s_removed[tid] = 0u;
   if (tid < 16) s_rem[tid] = 0u;
   if (tid < 2) s_status[tid] = 0;
-  if (tid < 4) s_local[tid] = 0;
   asm volatile("griddepcontrol.launch_dependents;");
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  for (int i = tid; i < kBins; i += blockDim.x) s_bins[i] = 0;
+  s_bins[tid] = 0;  // kBins == blockDim.x
   __syncthreads();
   FZ_STAMP(0);
   FZ_STAMP(1);
 
-  // ---- P1: decode + clip + min-size filter (proposal.py:77-120); keys stay in registers ----
+  // ---- P1: decode + clip + min-size filter (proposal.py:77-120); score keys go to shared memory ----
   const int hwc = dg.hc * dg.wc;
   const size_t hw = (size_t)dg.H * dg.W;
   const float* fg = g.cls_prob + (size_t)b * pg.cls_img_stride + pg.cls_fg_offset;
@@ -205,17 +282,20 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   const int chunk = (pg.n_crop + csize - 1) / csize;
   const int q_begin = rank * chunk;
   const int q_end = min(q_begin + chunk, pg.n_crop);
-  const float rcp_hwc = 1.0f / (float)hwc, rcp_wc = 1.0f / (float)dg.wc;
-  u32 rk[ITEMS];
+  const float rcp_hwc = 1.0f / (float)hwc, rcp_wc = 1.0f / (float)dg.wc, rcp_A = 1.0f / (float)dg.A;
+  const float lim_x = __fsub_rn(im_w, 1.0f), lim_y = __fsub_rn(im_h, 1.0f);
+  const float ms32 = __fmul_rn(g.min_size, im_s);  // proposal.py:117: an f32 product under numpy >= 2 (NEP 50)
+  const int items = g.items;
   {
-    int nnan = 0;
-    constexpr int kGroup = ITEMS < 4 ? ITEMS : 4;
+    bool nanflag = false;
+    // Two anchors per round: first ALL ten loads (independent of each other), then the arithmetic.  The loop is not
+    // unrolled further: code that runs once per launch costs an instruction-cache miss per line.
+#pragma unroll 1
+    for (int i0 = 0; i0 < items; i0 += 2) {
+      int ia[2], ih[2], iw[2];
+      float dx[2], dy[2], dw[2], dh[2], sc[2];
 #pragma unroll
-    for (int i0 = 0; i0 < ITEMS; i0 += kGroup) {
-      int ia[kGroup], ih[kGroup], iw[kGroup];
-      float dx[kGroup], dy[kGroup], dw[kGroup], dh[kGroup], sc[kGroup];
-#pragma unroll
-      for (int j = 0; j < kGroup; ++j) {
+      for (int j = 0; j < 2; ++j) {
         const int q = q_begin + tid + (i0 + j) * 1024;
         ia[j] = -1;
         ih[j] = iw[j] = 0;
@@ -241,19 +321,23 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         }
       }
 #pragma unroll
-      for (int j = 0; j < kGroup; ++j) {
+      for (int j = 0; j < 2; ++j) {
         u32 key = 0;
-        bool nan = false;
         if (ia[j] >= 0) {
-          double bx[4];
-          decode_clip_values(g.at, dg, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], im_h, im_w, bx);
-          const bool valid = passes_min_size(bx, g.min_size, im_s);
-          nan = (sc[j] != sc[j]) || (dx[j] != dx[j]) || (dy[j] != dy[j]) || (dw[j] != dw[j]) || (dh[j] != dh[j]);
+          // min-size filter (proposal.py:113-120, 156-161) on the float32 image of the box; the reference's float64
+          // arithmetic decides only when a side is within the error bound of the threshold (or nothing is finite)
+          const Dec32 d = decode32_core(g, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], lim_x, lim_y);
+          const float ws = (d.x2 - d.x1) + 1.0f, hs = (d.y2 - d.y1) + 1.0f;
+          const float m = 2.0f * d.e + 2.3841858e-07f * (fmaxf(ws, hs) + 1.0f);  // 2e + 2^-22 (side + 1)
+          const float lo = fminf(ws, hs) - ms32;
+          bool valid = lo > m;
+          if (!valid && !(lo < -m)) valid = exact_min_size(g, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], im_h, im_w, im_s);
+          // the clip drops NaNs, so the reference's NaN check (proposal.py:58-62) looks at the raw values
+          nanflag |= (sc[j] != sc[j]) || (dx[j] != dx[j]) || (dy[j] != dy[j]) || (dw[j] != dw[j]) || (dh[j] != dh[j]);
           key = valid ? score_key32(sc[j]) : 0u;
         }
-        rk[i0 + j] = key;
+        s_keys[(i0 + j) * 1024 + tid] = key;
         if (key != 0u) atomicAdd(&s_bins[bin_of_key(key)], 1u);
-        nnan += __popc(__ballot_sync(0xffffffffu, nan));
       }
     }
     if (pg.cropped) {  // proposal.py:58-62 checks the whole arrays, cropped or not
@@ -261,20 +345,18 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       for (int q = rank * fchunk + tid; q < min((rank + 1) * fchunk, pg.n_full); q += 1024) {
         const float v0 = __ldg(fg + q), v1 = __ldg(deltas + q), v2 = __ldg(deltas + q + pg.n_full);
         const float v3 = __ldg(deltas + q + 2 * (size_t)pg.n_full), v4 = __ldg(deltas + q + 3 * (size_t)pg.n_full);
-        if ((v0 != v0) || (v1 != v1) || (v2 != v2) || (v3 != v3) || (v4 != v4)) nnan = 1;
+        nanflag |= (v0 != v0) || (v1 != v1) || (v2 != v2) || (v3 != v3) || (v4 != v4);
       }
-      nnan = __popc(__ballot_sync(0xffffffffu, nnan != 0));
     }
-    if (lane == 0 && nnan) atomicAdd(&s_local[1], nnan);
-    __syncthreads();
-    if (tid == 0) s_pub[0] = s_local[1];
+    const int any_nan = __syncthreads_or(nanflag ? 1 : 0);
+    if (tid == 0) s_pub[0] = any_nan;
     if (tid < kBins / 2) s_pack[tid] = s_bins[2 * tid] | (s_bins[2 * tid + 1] << 16);
     {  // coarse counts: warp w sums fine bins 32w .. 32w+31
       const u32 v = __reduce_add_sync(0xffffffffu, s_bins[warp * 32 + lane]);
       if (lane == 0) s_cpub[warp] = v;
     }
   }
-  cluster.sync();  // ONE barrier ends the decode phase: NaN counts and bin tables of every CTA are published
+  cluster.sync();  // ONE barrier ends the decode phase: NaN flags and bin tables of every CTA are published
   FZ_STAMP(2);
 
   // ---- P2: cluster-wide coarse table, pre-NMS cut, window plan ----
@@ -312,158 +394,131 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   const int c_w0 = s_plan[1];   // lowest coarse bin of the first window
   FZ_STAMP(3);
 
-  // ---- materialise the candidates of coarse bins [c_lo, c_hi]: fine table (DSMEM pull), bucket starts, scatter ----
-  u64* comp = g.comp + (size_t)b * pg.n_crop;
-  int lo_mat = kBins;  // lowest fine bin materialised so far
-  auto materialize = [&](int c_lo, int c_hi) {
-    const int top = 32 * c_hi + 31, bot = 32 * c_lo;
-    const int npair = 16 * (c_hi - c_lo + 1);  // thread t < npair owns bins hi = top - 2t and lo = hi - 1
-    const bool owner = tid < npair;
-    const int bhi = top - 2 * tid, blo = bhi - 1;
-    u32 n_hi = 0, n_lo = 0, pre_hi = 0, pre_lo = 0;
-    if (owner) {
-      for (int r0 = 0; r0 < csize; r0 += 8) {
-        u32 v[8];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          const int o = rank + r0 + r, src = o < csize ? o : o - csize;
-          v[r] = (r0 + r < csize) ? cluster.map_shared_rank(s_pack, src)[blo >> 1] : 0u;
-        }
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          const int o = rank + r0 + r, src = o < csize ? o : o - csize;
-          n_lo += v[r] & 0xffffu;
-          n_hi += v[r] >> 16;
-          if (r0 + r < csize && src < rank) {
-            pre_lo += v[r] & 0xffffu;
-            pre_hi += v[r] >> 16;
-          }
-        }
-      }
-    }
-    // block-wide exclusive scan of (n_hi + n_lo) in thread order = descending bins
-    u32 incl = n_hi + n_lo;
-    for (int o = 1; o < 32; o <<= 1) {
-      const u32 v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    if (lane == 31) s_scan[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-      u32 w = s_scan[lane];
-      for (int o = 1; o < 32; o <<= 1) {
-        const u32 v = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += v;
-      }
-      s_scan[lane] = w;  // inclusive over warps
-    }
-    __syncthreads();
-    const u32 before = (warp > 0 ? s_scan[warp - 1] : 0u) + incl - (n_hi + n_lo);
-    if (owner) {
-      const u32 base_hi = s_csuf[c_hi] + before, base_lo = base_hi + n_hi;
-      const bool in_hi = base_hi < (u32)k, in_lo = base_lo < (u32)k;  // bins below the pre-NMS cut stay empty
-      s_base[bhi] = base_hi;
-      s_base[blo] = base_lo;
-      s_cnt[bhi] = in_hi ? n_hi : 0u;
-      s_cnt[blo] = in_lo ? n_lo : 0u;
-      s_own[bhi] = base_hi + pre_hi;
-      s_own[blo] = base_lo + pre_lo;
-      s_bins[bhi] = 0u;
-      s_bins[blo] = 0u;
-      if (in_hi && (u32)k <= base_hi + n_hi) {
-        s_plan[2] = bhi;
-        s_plan[3] = k - (int)base_hi;
-      }
-      if (in_lo && (u32)k <= base_lo + n_lo) {
-        s_plan[2] = blo;
-        s_plan[3] = k - (int)base_lo;
-      }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const u32 key = rk[i];
-      if (key != 0u) {
-        const int bin = bin_of_key(key);
-        if (bin >= bot && bin <= top && s_cnt[bin] != 0u) {
-          const u32 slot = s_own[bin] + atomicAdd(&s_bins[bin], 1u);
-          const u32 p = (u32)q_to_p(q_begin + tid + i * 1024, hwc, dg.A);
-          comp[slot] = ((u64)key << 32) | (u32)(~p);
-        }
-      }
-    }
-    lo_mat = (c_lo == cc) ? s_plan[2] : bot;
-    cluster.sync();  // the window's composites are visible to every CTA of the cluster
-  };
-
   // ---- greedy NMS over the bucketed list ----
-  const float lim_x = __fsub_rn(im_w, 1.0f), lim_y = __fsub_rn(im_h, 1.0f);
+  u64* comp = g.comp + (size_t)b * pg.n_crop;
   const bool screen_ok = g.thr > 0.0 && g.thr < 1.0;
   const float c32 = screen_ok ? (float)(g.thr / (1.0 + g.thr)) : 0.0f;
   float4* kbox = g.kbox + (size_t)b * g.keep_cap;
   float4* kaux = g.kaux + (size_t)b * g.keep_cap;
-  int nk = 0, fin = 0, stripes = 0;
+  int nk = 0, fin = 0;
   int c0 = 0;          // next raw slot
   int windows = 0;     // windows materialised
+  int lo_mat = kBins;  // lowest fine bin materialised so far
   int ps_bin = -1;     // bucket currently ordered in place (too large to be ranked by counting)
   int ps_end = 0;      // end of its selected part
-  u32 pairs = 0;
-  bool synced = false;  // a cluster barrier has been passed since the last remote shared-memory read
-  if (k > 0) {
-    materialize(c_w0, kCoarse - 1);
-    windows = 1;
-    synced = true;
-  }
-  FZ_STAMP(4);
-  FZ_STAMP(5);
-  FZ_STAMP(6);
+  u32 pairs = 0, n_und = 0;
   while (k > 0 && !fin && stripes < (1 << 20)) {
-    int mat_end = (int)(s_base[lo_mat] + s_cnt[lo_mat]);
-    if (c0 >= mat_end) {
-      if (windows == 1 && c_w0 > cc) {
-        materialize(cc, c_w0 - 1);
-        windows = 2;
-        mat_end = (int)(s_base[lo_mat] + s_cnt[lo_mat]);
-        if (c0 >= mat_end) break;
-      } else {
-        break;
+    // ---- the candidate list is materialised in (at most) two windows of coarse bins, top scores first ----
+    if (windows == 0 || (c0 >= (int)s_end[lo_mat] && windows == 1 && c_w0 > cc)) {
+      const int c_lo = windows == 0 ? c_w0 : cc, c_hi = windows == 0 ? kCoarse - 1 : c_w0 - 1;
+      // fine table of the window's bins (DSMEM pull), bucket starts, scatter of this CTA's composites
+      const int top = 32 * c_hi + 31, bot = 32 * c_lo;
+      const int npair = 16 * (c_hi - c_lo + 1);  // thread t < npair owns bins hi = top - 2t and lo = hi - 1
+      const bool owner = tid < npair;
+      const int bhi = top - 2 * tid, blo = bhi - 1;
+      u32 n_hi = 0, n_lo = 0, pre_hi = 0, pre_lo = 0;
+      if (owner) {
+#pragma unroll 1
+        for (int r0 = 0; r0 < csize; r0 += 8) {
+          u32 v[8];
+#pragma unroll
+          for (int r = 0; r < 8; ++r) {
+            const int o = rank + r0 + r, src = o < csize ? o : o - csize;
+            v[r] = (r0 + r < csize) ? cluster.map_shared_rank(s_pack, src)[blo >> 1] : 0u;
+          }
+#pragma unroll
+          for (int r = 0; r < 8; ++r) {
+            const int o = rank + r0 + r, src = o < csize ? o : o - csize;
+            n_lo += v[r] & 0xffffu;
+            n_hi += v[r] >> 16;
+            if (r0 + r < csize && src < rank) {
+              pre_lo += v[r] & 0xffffu;
+              pre_hi += v[r] >> 16;
+            }
+          }
+        }
+      }
+      // block-wide exclusive scan of (n_hi + n_lo) in thread order = descending bins
+      u32 incl = n_hi + n_lo;
+      for (int o = 1; o < 32; o <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) s_scan[warp] = incl;
+      __syncthreads();
+      if (warp == 0) {
+        u32 w = s_scan[lane];
+        for (int o = 1; o < 32; o <<= 1) {
+          const u32 v = __shfl_up_sync(0xffffffffu, w, o);
+          if (lane >= o) w += v;
+        }
+        s_scan[lane] = w;  // inclusive over warps
+      }
+      __syncthreads();
+      const u32 before = (warp > 0 ? s_scan[warp - 1] : 0u) + incl - (n_hi + n_lo);
+      if (owner) {
+        const u32 base_hi = s_csuf[c_hi] + before, base_lo = base_hi + n_hi;
+        const bool in_hi = base_hi < (u32)k, in_lo = base_lo < (u32)k;  // bins below the pre-NMS cut stay empty
+        s_base[bhi] = base_hi;
+        s_base[blo] = base_lo;
+        s_cnt[bhi] = in_hi ? n_hi : 0u;
+        s_cnt[blo] = in_lo ? n_lo : 0u;
+        s_end[bhi] = base_hi + (in_hi ? n_hi : 0u);
+        s_end[blo] = base_lo + (in_lo ? n_lo : 0u);
+        s_own[bhi] = base_hi + pre_hi;
+        s_own[blo] = base_lo + pre_lo;
+        s_bins[bhi] = 0u;
+        s_bins[blo] = 0u;
+        if (in_hi && (u32)k <= base_hi + n_hi) {
+          s_plan[2] = bhi;
+          s_plan[3] = k - (int)base_hi;
+        }
+        if (in_lo && (u32)k <= base_lo + n_lo) {
+          s_plan[2] = blo;
+          s_plan[3] = k - (int)base_lo;
+        }
+      }
+      __syncthreads();
+#pragma unroll 1
+      for (int i = 0; i < items; ++i) {
+        const u32 key = s_keys[i * 1024 + tid];
+        if (key != 0u) {
+          const int bin = bin_of_key(key);
+          if (bin >= bot && bin <= top && s_cnt[bin] != 0u) {
+            const u32 slot = s_own[bin] + atomicAdd(&s_bins[bin], 1u);
+            const int q = q_begin + tid + i * 1024;
+            const int a = fast_div(q, hwc, rcp_hwc);
+            const u32 p = (u32)((q - a * hwc) * dg.A + a);  // row index of the reference: (h * wc + w) * A + a
+            comp[slot] = ((u64)key << 32) | (u32)(~p);
+          }
+        }
+      }
+      lo_mat = (c_lo == cc) ? s_plan[2] : bot;
+      ++windows;
+      cluster.sync();  // the window's composites are visible to every CTA of the cluster
+      if (windows == 1) {
+        FZ_STAMP(4);
+        FZ_STAMP(5);
+        FZ_STAMP(6);
       }
     }
+    const int mat_end = (int)s_end[lo_mat];
+    if (c0 >= mat_end) break;
+    FZ_CLK(0);
     const int W = stripes == 0 ? g.first_stripe : g.next_stripe;
     const int cut_bin = (windows == 2 || c_w0 == cc) ? s_plan[2] : -1;
     const int r_cut = s_plan[3];
     // ---- plan the stripe [c0, c1): whole buckets, at most W raw slots ----
     int c1, n_s;
-    bool presorted = false;
-    if (ps_bin >= 0 && c0 < ps_end) {
-      presorted = true;
-    } else {
-      int lo = lo_mat, hi = kBins;
-      const u32 lim = (u32)(c0 + W);
-      while (lo < hi) {  // first bin whose bucket ends at or before c0 + W
-        const int mid = (lo + hi) >> 1;
-        if (s_base[mid] + s_cnt[mid] <= lim) hi = mid;
-        else lo = mid + 1;
-      }
-      c1 = lo < kBins ? (int)(s_base[lo] + s_cnt[lo]) : 0;
-      if (c1 <= c0) {
-        // the bucket that starts at c0 holds more than W candidates (scores crowded into one bin): the leader orders
-        // it in place with a sort in global memory -- first by the selection order (score desc, row desc:
-        // proposal.py:123-125) to apply the pre-NMS cut, then by the processing order (score desc, row asc: nms.py:19)
+    bool presorted = ps_bin >= 0 && c0 < ps_end;
+    if (!presorted) {
+      const int lo = first_bin_ending_by(s_end, lo_mat, (u32)(c0 + W), lane);
+      c1 = lo < kBins ? (int)s_end[lo] : 0;
+      if (c1 <= c0) {  // the bucket that starts at c0 holds more than W candidates (scores crowded into one bin)
         const int x = lo - 1;
         const int m = (int)s_cnt[x], base = (int)s_base[x];
         const int r = (x == cut_bin) ? r_cut : m;
-        if (rank == 0) {
-          u64* sb = g.sortbuf + (size_t)b * g.sort_cap;
-          const int n_pow2 = max(2, (int)(1u << (32 - __clz(max(m, 2) - 1))));
-          for (int i = tid; i < n_pow2; i += blockDim.x) sb[i] = i < m ? (__ldcg(comp + base + i) ^ 0xffffffffull) : 0ull;
-          __syncthreads();
-          bitonic_sort_desc_u64(sb, n_pow2);
-          for (int i = tid; i < n_pow2; i += blockDim.x) sb[i] = i < r ? (sb[i] ^ 0xffffffffull) : 0ull;
-          __syncthreads();
-          bitonic_sort_desc_u64(sb, n_pow2);
-          for (int i = tid; i < r; i += blockDim.x) comp[base + i] = sb[i];
-        }
+        if (rank == 0) presort_bucket(comp + base, m, r, g.sortbuf + (size_t)b * g.sort_cap);
         cluster.sync();
         ps_bin = x;
         ps_end = base + r;
@@ -475,10 +530,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       n_s = c1 - c0;
     } else {
       n_s = c1 - c0;
-      if (cut_bin >= 0 && (int)(s_base[cut_bin] + s_cnt[cut_bin]) <= c1 && (int)s_base[cut_bin] >= c0)
-        n_s -= (int)s_cnt[cut_bin] - r_cut;
+      if (cut_bin >= 0 && (int)s_end[cut_bin] <= c1 && (int)s_base[cut_bin] >= c0) n_s -= (int)s_cnt[cut_bin] - r_cut;
     }
     const int m_raw = c1 - c0;
+    FZ_CLK(1);
     // ---- stage the stripe: composites -> exact order inside each bucket -> float32 boxes ----
     {
       u64 c = 0ull;
@@ -488,9 +543,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         c = __ldcg(comp + c0 + tid);
         s_comp[tid] = c;
         p = (int)(~(u32)c);
-        aa = p % dg.A;
-        const int r = p / dg.A;
-        ah = r / dg.wc;
+        const int r = fast_div(p, dg.A, rcp_A);
+        aa = p - r * dg.A;
+        ah = fast_div(r, dg.wc, rcp_wc);
         aw = r - ah * dg.wc;
         const float* d = deltas + ((size_t)aa * 4) * hw + (size_t)ah * dg.W + aw;
         dx = __ldg(d);
@@ -499,7 +554,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         dh = __ldg(d + 3 * hw);
       }
       if (tid < 16) s_rem[tid] = 0u;
+      FZ_CLK(2);
       __syncthreads();
+      FZ_CLK(3);
       if (tid < m_raw) {
         int pos = tid, kpos = -1 - (c0 + tid);  // ordered in place: the position in the pre-NMS order is found on output
         bool selected = true;
@@ -507,24 +564,38 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           const u32 key = (u32)(c >> 32);
           const int bin = bin_of_key(key);
           const int bs = (int)s_base[bin] - c0, bn = (int)s_cnt[bin];
-          int n_gt = 0, n_eq_lt = 0, n_eq_gt = 0;
-          for (int j = 0; j < bn; ++j) {
-            const u64 o = s_comp[bs + j];
-            if ((u32)(o >> 32) != key) {
-              n_gt += o > c ? 1 : 0;
-            } else {  // equal scores: composites hold ~row
-              n_eq_lt += (u32)o > (u32)c ? 1 : 0;
-              n_eq_gt += (u32)o < (u32)c ? 1 : 0;
+          // count, inside the bucket, the composites that come first (greater score, or equal score and smaller row:
+          // composites hold ~row) and the ones with the same score; equal scores are rare and take the second loop
+          int n_first = 0, n_eq_tot = 0;
+          const u64* bk = s_comp + bs;
+          int j = 0;
+          for (; j + 4 <= bn; j += 4) {
+            const u64 o0 = bk[j], o1 = bk[j + 1], o2 = bk[j + 2], o3 = bk[j + 3];
+            n_first += (o0 > c ? 1 : 0) + (o1 > c ? 1 : 0) + (o2 > c ? 1 : 0) + (o3 > c ? 1 : 0);
+            n_eq_tot += ((u32)(o0 >> 32) == key ? 1 : 0) + ((u32)(o1 >> 32) == key ? 1 : 0) +
+                        ((u32)(o2 >> 32) == key ? 1 : 0) + ((u32)(o3 >> 32) == key ? 1 : 0);
+          }
+          for (; j < bn; ++j) {
+            const u64 o = bk[j];
+            n_first += o > c ? 1 : 0;
+            n_eq_tot += (u32)(o >> 32) == key ? 1 : 0;
+          }
+          int n_eq_lt = 0;
+          if (n_eq_tot > 1) {
+            for (j = 0; j < bn; ++j) {
+              const u64 o = bk[j];
+              n_eq_lt += ((u32)(o >> 32) == key && (u32)o > (u32)c) ? 1 : 0;
             }
           }
+          const int n_gt = n_first - n_eq_lt, n_eq_gt = n_eq_tot - 1 - n_eq_lt;
           const int r_b = (bin == cut_bin) ? r_cut : bn;
           const int sel_rank = n_gt + n_eq_gt;  // (score desc, row desc): proposal.py:123-125 with the documented tie rule
           selected = sel_rank < r_b;
-          const int n_eq_tot = n_eq_lt + n_eq_gt + 1;
           const int n_sel_run = min(n_eq_tot, r_b - n_gt);
           pos = bs + n_gt + n_eq_lt - (n_eq_tot - n_sel_run);  // (score desc, row asc): nms.py:19 re-sorts the list
           kpos = (int)s_base[bin] + sel_rank;
         }
+        FZ_CLK(4);
         if (selected) {
           const Box32 bx = decode32(g, dx, dy, dw, dh, ah, aw, aa, lim_x, lim_y, c32);
           s_cbox[pos] = make_float4(bx.x1, bx.y1, bx.x2p, bx.y2p);
@@ -533,7 +604,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           s_kpos[pos] = kpos;
         }
       }
+      FZ_CLK(5);
       __syncthreads();
+      FZ_CLK(6);
     }
     if (stripes == 0) FZ_STAMP(10);
     // ---- IoU bit blocks of 32 x 32 pairs: in-stripe lower triangle + (kept so far) x stripe ----
@@ -541,103 +614,102 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       const int n_cg = (n_s + 31) >> 5, n_rg = (nk + 31) >> 5;
       const int n_tri = n_cg * (n_cg + 1) / 2;
       const int n_tasks = n_tri + n_rg * n_cg;
+#pragma unroll 1
       for (int u = warp * csize + rank; u < n_tasks; u += 32 * csize) {
-        if (u < n_tri) {
+        const bool tri = u < n_tri;
+        int cg, ri;      // column group; row = stripe position (tri) or index into the kept list (cross)
+        u32 mask = 0xffffffffu;
+        Box32 r;
+        if (tri) {
           int rb = (int)((sqrtf(8.0f * (float)u + 1.0f) - 1.0f) * 0.5f);
           while (rb * (rb + 1) / 2 > u) --rb;
           while ((rb + 1) * (rb + 2) / 2 <= u) ++rb;
-          const int cb = u - rb * (rb + 1) / 2;
-          const int i = rb * 32 + lane;
-          const bool live = i < n_s;
-          Box32 r;
-          {
-            const float4 v = s_cbox[live ? i : 0];
-            const float2 a = s_caux[live ? i : 0];
-            r.x1 = v.x;
-            r.y1 = v.y;
-            r.x2p = v.z;
-            r.y2p = v.w;
-            r.a = a.x;
-            r.t = a.y;
-          }
-          const int jn = min(32, n_s - cb * 32);
-          u32 supp = 0, und = 0;
-#pragma unroll 4
-          for (int j = 0; j < jn; ++j) pair32(r, s_cbox[cb * 32 + j], s_caux[cb * 32 + j], j, supp, und);
-          u32 mask = live ? 0xffffffffu : 0u;
-          if (cb == rb) mask &= (1u << lane) - 1u;  // diagonal block: strictly below the diagonal
-          supp &= mask;
-          und &= mask;
-          if (g.pair_count) pairs += __popc(mask & (jn == 32 ? 0xffffffffu : ((1u << jn) - 1u)));
-          while (und) {
-            const int j = __ffs(und) - 1;
-            und &= und - 1u;
-            if (exact_pair(g, deltas, im_h, im_w, s_p[i], s_p[cb * 32 + j])) supp |= 1u << j;
-            else supp &= ~(1u << j);
-          }
-          if (live) L_M[i * kMPitch + cb] = supp;
+          cg = u - rb * (rb + 1) / 2;
+          ri = rb * 32 + lane;
+          if (cg == rb) mask = (1u << lane) - 1u;  // diagonal block: strictly below the diagonal
+          if (ri >= n_s) mask = 0u;
+          const float4 v = s_cbox[ri < n_s ? ri : 0];
+          const float2 a = s_caux[ri < n_s ? ri : 0];
+          r.x1 = v.x;
+          r.y1 = v.y;
+          r.x2p = v.z;
+          r.y2p = v.w;
+          r.a = a.x;
+          r.t = a.y;
         } else {
           const int v = u - n_tri;
-          const int rg = v / n_cg, cg = v - rg * n_cg;
-          const int ki = rg * 32 + lane;
-          const bool live = ki < nk;
-          Box32 r;
-          int p_row;
-          {
-            const float4 v4 = __ldcg(kbox + (live ? ki : 0));
-            const float4 a4 = __ldcg(kaux + (live ? ki : 0));
-            r.x1 = v4.x;
-            r.y1 = v4.y;
-            r.x2p = v4.z;
-            r.y2p = v4.w;
-            r.a = a4.x;
-            r.t = a4.y;
-            p_row = __float_as_int(a4.z);
-          }
-          const int jn = min(32, n_s - cg * 32);
-          u32 supp = 0, und = 0;
-#pragma unroll 4
-          for (int j = 0; j < jn; ++j) pair32(r, s_cbox[cg * 32 + j], s_caux[cg * 32 + j], j, supp, und);
-          if (!live) supp = und = 0u;
-          if (g.pair_count && live) pairs += jn;
-          while (und) {
+          const int rg = v / n_cg;
+          cg = v - rg * n_cg;
+          ri = rg * 32 + lane;
+          if (ri >= nk) mask = 0u;
+          const float4 v4 = __ldcg(kbox + (ri < nk ? ri : 0));
+          const float4 a4 = __ldcg(kaux + (ri < nk ? ri : 0));
+          r.x1 = v4.x;
+          r.y1 = v4.y;
+          r.x2p = v4.z;
+          r.y2p = v4.w;
+          r.a = a4.x;
+          r.t = a4.y;
+        }
+        const int jn = min(32, n_s - cg * 32);
+        if (jn < 32) mask &= (1u << jn) - 1u;
+        u32 supp, und;
+        block_bits(r, s_cbox + cg * 32, s_caux + cg * 32, jn, supp, und);
+        supp &= mask;
+        und &= mask;
+        if (g.pair_count) {
+          pairs += __popc(mask);
+          n_und += __popc(und);
+        }
+        if (und) {  // rare: the reference's float64 arithmetic decides
+          const int p_row = tri ? s_p[ri] : __float_as_int(__ldcg(kaux + ri).z);
+          do {
             const int j = __ffs(und) - 1;
             und &= und - 1u;
             if (exact_pair(g, deltas, im_h, im_w, p_row, s_p[cg * 32 + j])) supp |= 1u << j;
             else supp &= ~(1u << j);
-          }
+          } while (und);
+        }
+        if (tri) {
+          if (ri < n_s) L_M[ri * kMPitch + cg] = supp;
+        } else {
           supp = __reduce_or_sync(0xffffffffu, supp);
           if (lane == 0 && supp) atomicOr(&s_rem[cg], supp);
         }
       }
+      FZ_CLK(7);
       __syncthreads();
+      FZ_CLK(8);
       if (tid < 16 && s_rem[tid]) atomicOr(L_removed + tid, s_rem[tid]);
     }
     if (stripes == 0) FZ_STAMP(11);
     cluster.sync();  // the stripe's bit rows and removed words are complete in the leader's shared memory
-    // ---- leader: resolve the stripe as one fixed point of  keep_i = alive_i and no kept j < i suppresses i ----
     if (stripes == 0) FZ_STAMP(12);
+    FZ_CLK(9);
+    // ---- leader: resolve the stripe as one fixed point of  keep_i = alive_i and no kept j < i suppresses i ----
     if (rank == 0) {
-      const int nw = (n_s + 31) >> 5;
       if (tid < 16) {
         const int left = n_s - tid * 32;
         const u32 valid = left >= 32 ? 0xffffffffu : (left > 0 ? (1u << left) - 1u : 0u);
         s_keep[tid] = ~s_removed[tid] & valid;
         s_removed[tid] = 0u;
       }
+      // this thread's bit row in registers (words up to its own; the words above the diagonal are never written)
+      u32 rw[16];
+#pragma unroll
+      for (int w = 0; w < 16; ++w) rw[w] = (tid < n_s && w <= warp) ? s_M[tid * kMPitch + w] : 0u;
       __syncthreads();
+      FZ_CLK(10);
       const bool alive = tid < n_s && ((s_keep[tid >> 5] >> lane) & 1u);
       int cur = 0;
       for (int it = 0; it <= n_s; ++it) {
-        bool mine = false;
-        if (alive) {
-          const u32* row = s_M + tid * kMPitch;
-          const u32* kp = s_keep + cur * 16;
-          u32 bad = 0;
-          for (int w = 0; w <= warp; ++w) bad |= row[w] & kp[w];
-          mine = bad == 0u;
-        }
-        const u32 bal = __ballot_sync(0xffffffffu, mine);
+        if (it < 8) FZ_CLK(12 + it);
+        const uint4* kp4 = reinterpret_cast<const uint4*>(s_keep + cur * 16);
+        const uint4 k0 = kp4[0], k1 = kp4[1], k2 = kp4[2], k3 = kp4[3];
+        const u32 bad = (rw[0] & k0.x) | (rw[1] & k0.y) | (rw[2] & k0.z) | (rw[3] & k0.w) | (rw[4] & k1.x) | (rw[5] & k1.y) |
+                        (rw[6] & k1.z) | (rw[7] & k1.w) | (rw[8] & k2.x) | (rw[9] & k2.y) | (rw[10] & k2.z) |
+                        (rw[11] & k2.w) | (rw[12] & k3.x) | (rw[13] & k3.y) | (rw[14] & k3.z) | (rw[15] & k3.w);
+        const u32 bal = __ballot_sync(0xffffffffu, alive && bad == 0u);
         bool changed = false;
         if (lane == 0 && warp < 16) {
           changed = bal != s_keep[cur * 16 + warp];
@@ -647,20 +719,28 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         if (!__syncthreads_or(changed)) break;
         if (g.dbg && tid == 0 && stripes == 0) g.dbg[(size_t)b * 16 + 15] = (u64)(it + 1);
       }
-      const u32* kp = s_keep + cur * 16;
+      FZ_CLK(20);
       int before = 0, total = 0;
-      for (int w = 0; w < nw; ++w) {
-        const int c = __popc(kp[w]);
-        if (w < warp) before += c;
-        total += c;
+      {
+        const uint4* kp4 = reinterpret_cast<const uint4*>(s_keep + cur * 16);
+        const uint4 k0 = kp4[0], k1 = kp4[1], k2 = kp4[2], k3 = kp4[3];
+        const u32 kw[16] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w, k2.x, k2.y, k2.z, k2.w, k3.x, k3.y, k3.z, k3.w};
+#pragma unroll
+        for (int w = 0; w < 16; ++w) {
+          const int c = __popc(kw[w]);
+          before += w < warp ? c : 0;
+          total += c;
+        }
       }
-      const bool mine = tid < n_s && ((kp[tid >> 5] >> lane) & 1u);
-      const int idx = nk + before + (tid < n_s ? __popc(kp[tid >> 5] & ((1u << lane) - 1u)) : 0);
+      const u32 myw = s_keep[cur * 16 + (warp & 15)];
+      const bool mine = tid < n_s && ((myw >> lane) & 1u);
+      const int idx = nk + before + __popc(myw & ((1u << lane) - 1u));
       if (mine && (g.max_keep <= 0 || idx < g.max_keep)) {
         kbox[idx] = s_cbox[tid];
         const float2 a = s_caux[tid];
         kaux[idx] = make_float4(a.x, a.y, __int_as_float(s_p[tid]), __int_as_float(s_kpos[tid]));
       }
+      FZ_CLK(21);
       int nk2 = nk + total, f = 0;
       if (g.max_keep > 0 && nk2 >= g.max_keep) {
         nk2 = g.max_keep;
@@ -670,11 +750,13 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       if (tid < csize) *reinterpret_cast<int2*>(cluster.map_shared_rank(s_status, tid)) = make_int2(nk2, f);
     }
     if (stripes == 0) FZ_STAMP(13);
+    FZ_CLK(22);
     cluster.sync();
+    FZ_CLK(23);
     nk = s_status[0];
     fin = s_status[1];
     ++stripes;
-    c0 = presorted ? (c1 >= ps_end ? (int)(s_base[ps_bin] + s_cnt[ps_bin]) : c1) : c1;
+    c0 = presorted ? (c1 >= ps_end ? (int)s_end[ps_bin] : c1) : c1;
     if (presorted && ps_bin == cut_bin && c1 >= ps_end) break;
   }
   FZ_STAMP(7);
@@ -696,10 +778,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         const float4 a4 = __ldcg(kaux + j);
         const int p = __float_as_int(a4.z);
         int kpos = __float_as_int(a4.w);
-        const int a = p % dg.A, r = p / dg.A, h = r / dg.wc, w = r - h * dg.wc;
         if (o.rois) {
           double bx[4];
-          decode_clip(g.at, dg, deltas, h, w, a, im_h, im_w, bx);
+          exact_box(g, deltas, im_h, im_w, p, bx);
           float* ro = o.rois + (orow + j) * 5;
           ro[0] = (float)b;
           ro[1] = (float)bx[0];
@@ -708,6 +789,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           ro[4] = (float)bx[3];
         }
         if (o.scores) {  // the score sits at the flat (H,W,A) index of the FULL map (quirk Q1)
+          const int r = fast_div(p, dg.A, rcp_A), a = p - r * dg.A;
           const int w2 = r % dg.W, h2 = r / dg.W;
           o.scores[orow + j] = __ldg(fg + (size_t)a * hw + (size_t)h2 * dg.W + w2);
         }
@@ -717,7 +799,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
             const int s = -1 - kpos;
             const u32 key = (u32)(__ldcg(comp + s) >> 32);
             const int bin = bin_of_key(key);
-            const int lo = (int)s_base[bin], hi = lo + ((bin == s_plan[2] && (windows == 2 || c_w0 == cc)) ? s_plan[3] : (int)s_cnt[bin]);
+            const int lo = (int)s_base[bin];
+            const int hi = lo + ((bin == s_plan[2] && (windows == 2 || c_w0 == cc)) ? s_plan[3] : (int)s_cnt[bin]);
             int rs_ = s, re_ = s + 1;
             while (rs_ > lo && (u32)(__ldcg(comp + rs_ - 1) >> 32) == key) --rs_;
             while (re_ < hi && (u32)(__ldcg(comp + re_) >> 32) == key) ++re_;
@@ -742,11 +825,13 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   }
   if (g.pair_count) {
     pairs = __reduce_add_sync(0xffffffffu, pairs);
-    if (lane == 0 && pairs) atomicAdd(g.pair_count + b, pairs);
+    n_und = __reduce_add_sync(0xffffffffu, n_und);
+    if (lane == 0 && pairs) atomicAdd(g.pair_count + 2 * b, pairs);
+    if (lane == 0 && n_und) atomicAdd(g.pair_count + 2 * b + 1, n_und);
   }
   // Nobody may leave while its shared memory can still be read by another CTA: the coarse tables are pulled right
   // after the decode barrier, and every later remote access is followed by a barrier of the walk.
-  if (!synced) cluster.sync();
+  if (windows == 0) cluster.sync();
   FZ_STAMP(8);
   if (g.dbg && rank == 0 && tid == 0) {
     g.dbg[(size_t)b * 16 + 9] = (u64)stripes;
@@ -754,9 +839,10 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   }
 }
 
-static inline size_t fused_smem_bytes() {
-  return (size_t)kWMax * (sizeof(float4) + sizeof(float2) + sizeof(u64) + 2 * sizeof(int)) + (16 + 16 + 32) * sizeof(u32) +
-         (size_t)kWMax * kMPitch * sizeof(u32) + 64;
+static inline size_t fused_smem_bytes(int items) {
+  const int items2 = (items + 1) / 2 * 2;
+  return (size_t)kWMax * (sizeof(float4) + sizeof(float2) + sizeof(u64) + 2 * sizeof(int)) + (16 + 16) * sizeof(u32) +
+         (size_t)kWMax * kMPitch * sizeof(u32) + (size_t)items2 * 1024 * sizeof(u32) + 64;
 }
 
 }  // namespace fz

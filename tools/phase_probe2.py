@@ -64,8 +64,21 @@ for i in range(1, 9):
 d = s[:, [10, 11, 12, 13]] - s[:, [6, 10, 11, 12]]
 for nm, v in zip(("first stripe: staged", "bit blocks", "barrier", "resolve"), d.mean(axis=0)):
     print("    %-40s %7.2f us" % (nm, v * 1e-3))
+clk = s[:, 16:48]
+cn = ["loop top", "planned", "loads issued", "sync1 (comps in smem)", "ranked", "decoded+stored", "sync2", "my blocks done",
+      "sync (CTA blocks done)", "barrier A passed", "keep init sync", "nz masks", "round0", "round1", "round2", "round3", "round4",
+      "round5", "round6", "round7", "rounds done", "kept stored", "status pushed", "barrier B passed"]
+prev = None
+for i, nm in enumerate(cn):
+    v = clk[:, i]
+    if (v == 0).all():
+        continue
+    if prev is not None:
+        print("      %-28s +%7.0f cycles" % (nm, (v - clk[:, prev]).mean()))
+    prev = i
 print("  stripes %.1f windows %.1f fixed-point rounds (first stripe) %.1f" % (m[9], m[14], m[15]))
 h.count_pairs(True)
 step()
 h.count_pairs(False)
-print("  IoU pairs evaluated per image: %.0f" % h.pairs_read(B).mean())
+pr = h.pairs_read(B)
+print("  IoU pairs evaluated per image: %.0f, of which settled in float64: %.1f" % (pr[:, 0].mean(), pr[:, 1].mean()))
