@@ -13,7 +13,8 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmxrcnn_b200.so")
+# MXRCNN_B200_LIB: another build of the same library (A/B measurements of kernel variants, tools/ab_build.py)
+LIB_PATH = os.environ.get("MXRCNN_B200_LIB") or os.path.join(_HERE, "libmxrcnn_b200.so")
 
 c_int_p = ctypes.POINTER(ctypes.c_int32)
 c_float_p = ctypes.POINTER(ctypes.c_float)

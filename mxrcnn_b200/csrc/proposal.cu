@@ -263,6 +263,10 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
   MXR_REQUIRE(csize != 0, MXR_ERR_CUDA, "proposal: no cluster size of the fused kernel fits this device");
   void (*kern)(const fz::FusedArgs) = fz::proposal_fused_kernel;
   fa->items = items;
+  {
+    const char* nr = getenv("MXRCNN_B200_NULL");
+    fa->null_run = (nr && nr[0] == '1') ? 1 : 0;
+  }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(L.B * csize);

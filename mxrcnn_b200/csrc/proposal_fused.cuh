@@ -25,10 +25,14 @@
 namespace mxr {
 namespace fz {
 
+#ifndef FZ_P1_GROUP
+#define FZ_P1_GROUP 4  // anchors per decode round (loads first, then arithmetic)
+#endif
 static const int kBins = 1024;              // fine linear score bins: bin(s) = clamp(int(s * 1024))
 static const int kCoarse = 32;              // coarse bins of 32 fine bins each
 static const int kWMax = 512;               // widest stripe
-static const int kMPitch = kWMax / 32 + 1;  // u32 words per bit row in the leader's shared memory
+static const int kMWords = kWMax / 32;      // u32 words per bit row; rows are stored word-major: M[word][row], so that a
+                                            // warp's 32 rows of one word are 128 contiguous bytes (one remote transaction)
 
 struct FusedArgs {
   ProposalGeom pg;
@@ -43,6 +47,7 @@ struct FusedArgs {
   int pre_nms;
   int max_keep;      // > 0: post_nms_top_n
   int items;         // score keys per thread: ceil(n_crop / (cluster size * 1024))
+  int null_run;      // MXRCNN_B200_NULL=1 (measurement only): leave right after the dependency wait
   int first_stripe;  // width of the first stripe (multiple of 32, <= kWMax)
   int next_stripe;   // width of the later stripes
   int window0;       // candidates the first window should hold
@@ -159,14 +164,21 @@ __device__ __forceinline__ float pair_d(const Box32& r, const float4 cb, const f
 }
 __device__ __forceinline__ void block_bits(const Box32& r, const float4* __restrict__ cb, const float2* __restrict__ ca, int jn,
                                            u32& supp_out, u32& und_out) {
+  // groups of eight columns with compile-time bit positions; columns at and beyond jn (garbage inside the staging
+  // arrays, which are kWMax long) are masked off by the caller
   u32 supp = 0;
   bool any_und = false;
-#pragma unroll 4
-  for (int j = 0; j < jn; ++j) {
-    float tol;
-    const float d = pair_d(r, cb[j], ca[j], &tol);
-    supp |= (d > tol ? 1u : 0u) << j;
-    any_und = any_und || !(fabsf(d) > tol);
+#pragma unroll 1
+  for (int j0 = 0; j0 < jn; j0 += 8) {
+    u32 s8 = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float tol;
+      const float d = pair_d(r, cb[j0 + j], ca[j0 + j], &tol);
+      s8 |= d > tol ? (1u << j) : 0u;
+      any_und = any_und || !(fabsf(d) > tol);
+    }
+    supp |= s8 << j0;
   }
   u32 und = 0;
   if (any_und) {  // rare: find which
@@ -241,8 +253,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   __shared__ u32 s_scan[34];
   __shared__ int s_plan[8];           // 0 cut coarse bin, 1 first window's lowest coarse bin, 2 cut bin, 3 r_cut, 4 NaN count
   __shared__ int s_pub[2];            // this CTA's NaN flag (read by the other CTAs)
-  __shared__ __align__(8) int s_status[2];  // kept so far, quota reached: written by the leader into every CTA
-  __shared__ __align__(16) u32 s_keep[32];  // leader: [2][16] keep words (ping-pong)
+  __shared__ __align__(16) u32 s_keep[32];  // [2][16] keep words of the stripe being resolved (ping-pong)
+  __shared__ __align__(16) u32 s_kfin[16];  // keep words of the resolved stripe
   cgx::cluster_group cluster = cgx::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int csize = (int)cluster.num_blocks();
@@ -256,18 +268,18 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   u64* s_comp = reinterpret_cast<u64*>(s_caux + kWMax);                 // [kWMax] raw composites of the stripe
   int* s_p = reinterpret_cast<int*>(s_comp + kWMax);                    // [kWMax] row index
   int* s_kpos = s_p + kWMax;                                            // [kWMax] position in the pre-NMS order
-  u32* s_rem = reinterpret_cast<u32*>(s_kpos + kWMax);                  // [16] this CTA's share of the removed bits
-  u32* s_removed = s_rem + 16;                                          // leader: [16] removed by earlier stripes
-  u32* s_M = s_removed + 16;                                            // leader: [kWMax][kMPitch] bit rows
-  u32* s_keys = s_M + kWMax * kMPitch;                                  // [items (even)][1024] score keys, 0 = filtered out
-  u32* L_M = cluster.map_shared_rank(s_M, 0);
-  u32* L_removed = cluster.map_shared_rank(s_removed, 0);
+  u32* s_skey = reinterpret_cast<u32*>(s_kpos + kWMax);                 // [kWMax] score key
+  float4* s_roi = reinterpret_cast<float4*>(s_skey + kWMax);            // [kWMax / 2] output rows of this CTA's share of the stripe
+  u32* s_rem = reinterpret_cast<u32*>(s_roi + kWMax / 2);               // [16] this CTA's share of the removed bits
+  u32* s_removed = s_rem + 16;                                          // [2][16] removed by earlier stripes (stripe parity)
+  u32* s_M = s_removed + 32;                                            // [2][kMWords][kWMax] bit rows (stripe parity)
+  u32* s_keys = s_M + 2 * kWMax * kMWords;                              // [items rounded up to 4][1024] score keys, 0 = filtered out
   int stripes = 0;
-  if (rank == 0 && tid < 16) s_removed[tid] = 0u;
+  if (tid < 32) s_removed[tid] = 0u;
   if (tid < 16) s_rem[tid] = 0u;
-  if (tid < 2) s_status[tid] = 0;
   asm volatile("griddepcontrol.launch_dependents;");
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (g.null_run) return;  // launch + dependency floor of this configuration (tools/cluster_sweep2.py)
   s_bins[tid] = 0;  // kBins == blockDim.x
   __syncthreads();
   FZ_STAMP(0);
@@ -288,14 +300,14 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   const int items = g.items;
   {
     bool nanflag = false;
-    // Two anchors per round: first ALL ten loads (independent of each other), then the arithmetic.  The loop is not
-    // unrolled further: code that runs once per launch costs an instruction-cache miss per line.
+    // Four anchors per round: first ALL twenty loads (independent of each other: one DRAM round trip for an image of up
+    // to four keys per thread), then the arithmetic.
 #pragma unroll 1
-    for (int i0 = 0; i0 < items; i0 += 2) {
-      int ia[2], ih[2], iw[2];
-      float dx[2], dy[2], dw[2], dh[2], sc[2];
+    for (int i0 = 0; i0 < items; i0 += FZ_P1_GROUP) {
+      int ia[FZ_P1_GROUP], ih[FZ_P1_GROUP], iw[FZ_P1_GROUP];
+      float dx[FZ_P1_GROUP], dy[FZ_P1_GROUP], dw[FZ_P1_GROUP], dh[FZ_P1_GROUP], sc[FZ_P1_GROUP];
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
+      for (int j = 0; j < FZ_P1_GROUP; ++j) {
         const int q = q_begin + tid + (i0 + j) * 1024;
         ia[j] = -1;
         ih[j] = iw[j] = 0;
@@ -321,7 +333,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         }
       }
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
+      for (int j = 0; j < FZ_P1_GROUP; ++j) {
         u32 key = 0;
         if (ia[j] >= 0) {
           // min-size filter (proposal.py:113-120, 156-161) on the float32 image of the box; the reference's float64
@@ -417,24 +429,21 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       const bool owner = tid < npair;
       const int bhi = top - 2 * tid, blo = bhi - 1;
       u32 n_hi = 0, n_lo = 0, pre_hi = 0, pre_lo = 0;
-      if (owner) {
-#pragma unroll 1
-        for (int r0 = 0; r0 < csize; r0 += 8) {
-          u32 v[8];
+      if (owner) {  // all the cluster's tables in one round trip (a cluster has at most 16 CTAs)
+        u32 v[16];
 #pragma unroll
-          for (int r = 0; r < 8; ++r) {
-            const int o = rank + r0 + r, src = o < csize ? o : o - csize;
-            v[r] = (r0 + r < csize) ? cluster.map_shared_rank(s_pack, src)[blo >> 1] : 0u;
-          }
+        for (int r = 0; r < 16; ++r) {
+          const int o = rank + r, src = o < csize ? o : o - csize;
+          v[r] = r < csize ? cluster.map_shared_rank(s_pack, src)[blo >> 1] : 0u;
+        }
 #pragma unroll
-          for (int r = 0; r < 8; ++r) {
-            const int o = rank + r0 + r, src = o < csize ? o : o - csize;
-            n_lo += v[r] & 0xffffu;
-            n_hi += v[r] >> 16;
-            if (r0 + r < csize && src < rank) {
-              pre_lo += v[r] & 0xffffu;
-              pre_hi += v[r] >> 16;
-            }
+        for (int r = 0; r < 16; ++r) {
+          const int o = rank + r, src = o < csize ? o : o - csize;
+          n_lo += v[r] & 0xffffu;
+          n_hi += v[r] >> 16;
+          if (r < csize && src < rank) {
+            pre_lo += v[r] & 0xffffu;
+            pre_hi += v[r] >> 16;
           }
         }
       }
@@ -479,10 +488,13 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
         }
       }
       __syncthreads();
+      // bin(s) >= bot  <=>  s >= bot / 1024 (the bin function is monotone and bot / 1024 is exact), so most keys are
+      // turned away by one comparison
+      const u32 key_bot = bot == 0 ? 1u : score_key32((float)bot * (1.0f / (float)kBins));
 #pragma unroll 1
       for (int i = 0; i < items; ++i) {
         const u32 key = s_keys[i * 1024 + tid];
-        if (key != 0u) {
+        if (key >= key_bot) {
           const int bin = bin_of_key(key);
           if (bin >= bot && bin <= top && s_cnt[bin] != 0u) {
             const u32 slot = s_own[bin] + atomicAdd(&s_bins[bin], 1u);
@@ -564,21 +576,21 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           const u32 key = (u32)(c >> 32);
           const int bin = bin_of_key(key);
           const int bs = (int)s_base[bin] - c0, bn = (int)s_cnt[bin];
-          // count, inside the bucket, the composites that come first (greater score, or equal score and smaller row:
-          // composites hold ~row) and the ones with the same score; equal scores are rare and take the second loop
-          int n_first = 0, n_eq_tot = 0;
+          // count, inside the bucket, the greater scores and the equal ones; equal scores are rare and take the second
+          // loop, which counts the ones that come first among them (smaller row: composites hold ~row)
+          int n_gt = 0, n_eq_tot = 0;
           const u64* bk = s_comp + bs;
+          const u32* bk32 = reinterpret_cast<const u32*>(bk) + 1;  // score keys: the high words
           int j = 0;
           for (; j + 4 <= bn; j += 4) {
-            const u64 o0 = bk[j], o1 = bk[j + 1], o2 = bk[j + 2], o3 = bk[j + 3];
-            n_first += (o0 > c ? 1 : 0) + (o1 > c ? 1 : 0) + (o2 > c ? 1 : 0) + (o3 > c ? 1 : 0);
-            n_eq_tot += ((u32)(o0 >> 32) == key ? 1 : 0) + ((u32)(o1 >> 32) == key ? 1 : 0) +
-                        ((u32)(o2 >> 32) == key ? 1 : 0) + ((u32)(o3 >> 32) == key ? 1 : 0);
+            const u32 o0 = bk32[2 * j], o1 = bk32[2 * j + 2], o2 = bk32[2 * j + 4], o3 = bk32[2 * j + 6];
+            n_gt += (o0 > key ? 1 : 0) + (o1 > key ? 1 : 0) + (o2 > key ? 1 : 0) + (o3 > key ? 1 : 0);
+            n_eq_tot += (o0 == key ? 1 : 0) + (o1 == key ? 1 : 0) + (o2 == key ? 1 : 0) + (o3 == key ? 1 : 0);
           }
           for (; j < bn; ++j) {
-            const u64 o = bk[j];
-            n_first += o > c ? 1 : 0;
-            n_eq_tot += (u32)(o >> 32) == key ? 1 : 0;
+            const u32 o = bk32[2 * j];
+            n_gt += o > key ? 1 : 0;
+            n_eq_tot += o == key ? 1 : 0;
           }
           int n_eq_lt = 0;
           if (n_eq_tot > 1) {
@@ -587,7 +599,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
               n_eq_lt += ((u32)(o >> 32) == key && (u32)o > (u32)c) ? 1 : 0;
             }
           }
-          const int n_gt = n_first - n_eq_lt, n_eq_gt = n_eq_tot - 1 - n_eq_lt;
+          const int n_eq_gt = n_eq_tot - 1 - n_eq_lt;
           const int r_b = (bin == cut_bin) ? r_cut : bn;
           const int sel_rank = n_gt + n_eq_gt;  // (score desc, row desc): proposal.py:123-125 with the documented tie rule
           selected = sel_rank < r_b;
@@ -602,6 +614,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           s_caux[pos] = make_float2(bx.a, screen_ok ? bx.t : __int_as_float(0x7f800000));
           s_p[pos] = p;
           s_kpos[pos] = kpos;
+          s_skey[pos] = (u32)(c >> 32);
         }
       }
       FZ_CLK(5);
@@ -610,7 +623,23 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
     }
     if (stripes == 0) FZ_STAMP(10);
     // ---- IoU bit blocks of 32 x 32 pairs: in-stripe lower triangle + (kept so far) x stripe ----
+    const int par = stripes & 1;
+    u32* Mcur = s_M + par * (kWMax * kMWords);
+    u32* Rcur = s_removed + par * 16;
     {
+      // The output row of a stripe position (proposal.py:140-147: the reference's float64 box, cast to float32) is
+      // computed by the CTA that owns the position's group of 32 (group % cluster size) while the bit blocks are
+      // evaluated: the highest warps of a CTA have the fewest blocks.  After the stripe is resolved the owner only
+      // copies the rows of the kept positions out.
+      {
+        const int lg = 31 - warp;               // this warp's local group: positions (lg * csize + rank) * 32 + lane
+        const int pos = (lg * csize + rank) * 32 + lane;
+        if (lg < kWMax / 64 && pos < n_s && g.o.rois) {
+          double bx[4];
+          exact_box(g, deltas, im_h, im_w, s_p[pos], bx);
+          s_roi[lg * 32 + lane] = make_float4((float)bx[0], (float)bx[1], (float)bx[2], (float)bx[3]);
+        }
+      }
       const int n_cg = (n_s + 31) >> 5, n_rg = (nk + 31) >> 5;
       const int n_tri = n_cg * (n_cg + 1) / 2;
       const int n_tasks = n_tri + n_rg * n_cg;
@@ -671,7 +700,11 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           } while (und);
         }
         if (tri) {
-          if (ri < n_s) L_M[ri * kMPitch + cg] = supp;
+          if (ri < n_s) {  // every CTA resolves the stripe itself: the word goes into everybody's bit rows
+            u32* wp = Mcur + cg * kWMax + ri;
+#pragma unroll 1
+            for (int t = 0; t < csize; ++t) *cluster.map_shared_rank(wp, t) = supp;
+          }
         } else {
           supp = __reduce_or_sync(0xffffffffu, supp);
           if (lane == 0 && supp) atomicOr(&s_rem[cg], supp);
@@ -680,49 +713,77 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       FZ_CLK(7);
       __syncthreads();
       FZ_CLK(8);
-      if (tid < 16 && s_rem[tid]) atomicOr(L_removed + tid, s_rem[tid]);
+      if (tid < 16 * csize) {
+        const u32 v = s_rem[tid & 15];
+        if (v) atomicOr(cluster.map_shared_rank(Rcur + (tid & 15), tid >> 4), v);
+      }
     }
     if (stripes == 0) FZ_STAMP(11);
-    cluster.sync();  // the stripe's bit rows and removed words are complete in the leader's shared memory
+    // ONE barrier per stripe: the bit rows and removed words are complete in every CTA's shared memory.  The next
+    // stripe's words go to the other parity's buffers, so nobody overwrites rows that a slower CTA is still reading.
+    cluster.sync();
     if (stripes == 0) FZ_STAMP(12);
     FZ_CLK(9);
-    // ---- leader: resolve the stripe as one fixed point of  keep_i = alive_i and no kept j < i suppresses i ----
-    if (rank == 0) {
+    // ---- every CTA resolves the stripe: one fixed point of  keep_i = alive_i and no kept j < i suppresses i ----
+    {
       if (tid < 16) {
         const int left = n_s - tid * 32;
         const u32 valid = left >= 32 ? 0xffffffffu : (left > 0 ? (1u << left) - 1u : 0u);
-        s_keep[tid] = ~s_removed[tid] & valid;
-        s_removed[tid] = 0u;
+        s_keep[tid] = ~Rcur[tid] & valid;
+        Rcur[tid] = 0u;  // written again two stripes from now, after two more barriers
       }
-      // this thread's bit row in registers (words up to its own; the words above the diagonal are never written)
-      u32 rw[16];
-#pragma unroll
-      for (int w = 0; w < 16; ++w) rw[w] = (tid < n_s && w <= warp) ? s_M[tid * kMPitch + w] : 0u;
       __syncthreads();
       FZ_CLK(10);
-      const bool alive = tid < n_s && ((s_keep[tid >> 5] >> lane) & 1u);
-      int cur = 0;
-      for (int it = 0; it <= n_s; ++it) {
-        if (it < 8) FZ_CLK(12 + it);
-        const uint4* kp4 = reinterpret_cast<const uint4*>(s_keep + cur * 16);
-        const uint4 k0 = kp4[0], k1 = kp4[1], k2 = kp4[2], k3 = kp4[3];
-        const u32 bad = (rw[0] & k0.x) | (rw[1] & k0.y) | (rw[2] & k0.z) | (rw[3] & k0.w) | (rw[4] & k1.x) | (rw[5] & k1.y) |
-                        (rw[6] & k1.z) | (rw[7] & k1.w) | (rw[8] & k2.x) | (rw[9] & k2.y) | (rw[10] & k2.z) |
-                        (rw[11] & k2.w) | (rw[12] & k3.x) | (rw[13] & k3.y) | (rw[14] & k3.z) | (rw[15] & k3.w);
-        const u32 bal = __ballot_sync(0xffffffffu, alive && bad == 0u);
-        bool changed = false;
-        if (lane == 0 && warp < 16) {
-          changed = bal != s_keep[cur * 16 + warp];
-          s_keep[(cur ^ 1) * 16 + warp] = bal;
+      // Eight warps resolve the stripe, two bit rows per thread in registers (rows tid and tid + 256; words above the
+      // diagonal are never written and read as zero).  A round costs every participating warp ~50 instructions, so
+      // fewer warps with more rows each make a shorter round than one row per thread on sixteen warps.
+      if (warp < 8) {
+        u32 ra[8], rb[16];
+#pragma unroll
+        for (int w = 0; w < 8; ++w) ra[w] = (tid < n_s && w <= warp) ? Mcur[w * kWMax + tid] : 0u;
+#pragma unroll
+        for (int w = 0; w < 16; ++w) rb[w] = (tid + 256 < n_s && w <= warp + 8) ? Mcur[w * kWMax + tid + 256] : 0u;
+        const bool alive_a = tid < n_s && ((s_keep[warp] >> lane) & 1u);
+        const bool alive_b = tid + 256 < n_s && ((s_keep[8 + warp] >> lane) & 1u);
+        int cur = 0;
+        u32 bal_a = 0, bal_b = 0;
+        for (int it = 0; it <= n_s; ++it) {
+          if (it < 8) FZ_CLK(12 + it);
+          const uint4* kp4 = reinterpret_cast<const uint4*>(s_keep + cur * 16);
+          const uint4 k0 = kp4[0], k1 = kp4[1], k2 = kp4[2], k3 = kp4[3];
+          const u32 bad_a = (ra[0] & k0.x) | (ra[1] & k0.y) | (ra[2] & k0.z) | (ra[3] & k0.w) | (ra[4] & k1.x) | (ra[5] & k1.y) |
+                            (ra[6] & k1.z) | (ra[7] & k1.w);
+          const u32 bad_b = (rb[0] & k0.x) | (rb[1] & k0.y) | (rb[2] & k0.z) | (rb[3] & k0.w) | (rb[4] & k1.x) | (rb[5] & k1.y) |
+                            (rb[6] & k1.z) | (rb[7] & k1.w) | (rb[8] & k2.x) | (rb[9] & k2.y) | (rb[10] & k2.z) |
+                            (rb[11] & k2.w) | (rb[12] & k3.x) | (rb[13] & k3.y) | (rb[14] & k3.z) | (rb[15] & k3.w);
+          bal_a = __ballot_sync(0xffffffffu, alive_a && bad_a == 0u);
+          bal_b = __ballot_sync(0xffffffffu, alive_b && bad_b == 0u);
+          int changed = 0;
+          if (lane == 0) {
+            changed = (bal_a != s_keep[cur * 16 + warp] || bal_b != s_keep[cur * 16 + 8 + warp]) ? 1 : 0;
+            s_keep[(cur ^ 1) * 16 + warp] = bal_a;
+            s_keep[(cur ^ 1) * 16 + 8 + warp] = bal_b;
+          }
+          cur ^= 1;
+          int any;
+          asm volatile(
+              "{\n .reg .pred p, q;\n setp.ne.s32 p, %1, 0;\n bar.red.or.pred q, 1, 256, p;\n selp.s32 %0, 1, 0, q;\n}"
+              : "=r"(any)
+              : "r"(changed)
+              : "memory");
+          if (!any) break;
+          if (g.dbg && rank == 0 && tid == 0 && stripes == 0) g.dbg[(size_t)b * 16 + 15] = (u64)(it + 1);
         }
-        cur ^= 1;
-        if (!__syncthreads_or(changed)) break;
-        if (g.dbg && tid == 0 && stripes == 0) g.dbg[(size_t)b * 16 + 15] = (u64)(it + 1);
+        if (lane == 0) {  // the last round changed nothing: its ballots are the result
+          s_kfin[warp] = bal_a;
+          s_kfin[8 + warp] = bal_b;
+        }
       }
+      __syncthreads();
       FZ_CLK(20);
       int before = 0, total = 0;
       {
-        const uint4* kp4 = reinterpret_cast<const uint4*>(s_keep + cur * 16);
+        const uint4* kp4 = reinterpret_cast<const uint4*>(s_kfin);
         const uint4 k0 = kp4[0], k1 = kp4[1], k2 = kp4[2], k3 = kp4[3];
         const u32 kw[16] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w, k2.x, k2.y, k2.z, k2.w, k3.x, k3.y, k3.z, k3.w};
 #pragma unroll
@@ -732,35 +793,67 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
           total += c;
         }
       }
-      const u32 myw = s_keep[cur * 16 + (warp & 15)];
+      const u32 myw = s_kfin[warp & 15];
       const bool mine = tid < n_s && ((myw >> lane) & 1u);
       const int idx = nk + before + __popc(myw & ((1u << lane) - 1u));
-      if (mine && (g.max_keep <= 0 || idx < g.max_keep)) {
-        kbox[idx] = s_cbox[tid];
-        const float2 a = s_caux[tid];
-        kaux[idx] = make_float4(a.x, a.y, __int_as_float(s_p[tid]), __int_as_float(s_kpos[tid]));
-      }
-      FZ_CLK(21);
       int nk2 = nk + total, f = 0;
       if (g.max_keep > 0 && nk2 >= g.max_keep) {
         nk2 = g.max_keep;
         f = 1;
       }
-      // the result goes INTO every CTA's shared memory: after the barrier nobody reads remote shared memory
-      if (tid < csize) *reinterpret_cast<int2*>(cluster.map_shared_rank(s_status, tid)) = make_int2(nk2, f);
+      if (mine && (g.max_keep <= 0 || idx < g.max_keep)) {
+        if (!f) {
+          // rows of the later stripes' (kept so far) x stripe blocks.  Every CTA writes the SAME values to the same
+          // addresses and reads them back only after its own __syncthreads: no barrier between CTAs is needed.
+          kbox[idx] = s_cbox[tid];
+          const float2 a = s_caux[tid];
+          kaux[idx] = make_float4(a.x, a.y, __int_as_float(s_p[tid]), 0.0f);
+        }
+        const int lg = warp / csize;
+        if (warp - lg * csize == rank) {  // this CTA owns the position's group: results (proposal.py:140-149)
+          const NmsOutputs& o = g.o;
+          const size_t orow = (size_t)b * o.rows + idx;
+          if (o.rois) {
+            const float4 bx = s_roi[lg * 32 + lane];
+            float* ro = o.rois + orow * 5;
+            ro[0] = (float)b;
+            ro[1] = bx.x;
+            ro[2] = bx.y;
+            ro[3] = bx.z;
+            ro[4] = bx.w;
+          }
+          if (o.scores) {  // the staged key is an exact image of the float32 score (-0.0 reads back as +0.0)
+            const u32 key = s_skey[tid];
+            o.scores[orow] = __uint_as_float((key & 0x80000000u) ? (key & 0x7fffffffu) : ~key);
+          }
+          if (o.keep_orig) o.keep_orig[orow] = s_p[tid];
+          if (o.keep_pos) {
+            int kpos = s_kpos[tid];
+            if (kpos < 0) {  // bucket ordered in place: undo the tie-run reversal of nms.py:19 by looking at the neighbours
+              const int sl = -1 - kpos;
+              const u32 key = s_skey[tid];
+              const int bin = bin_of_key(key);
+              const int lo = (int)s_base[bin], hi = lo + ((bin == cut_bin) ? r_cut : (int)s_cnt[bin]);
+              int rs_ = sl, re_ = sl + 1;
+              while (rs_ > lo && (u32)(__ldcg(comp + rs_ - 1) >> 32) == key) --rs_;
+              while (re_ < hi && (u32)(__ldcg(comp + re_) >> 32) == key) ++re_;
+              kpos = rs_ + (re_ - 1 - sl);
+            }
+            o.keep_pos[orow] = kpos;
+          }
+        }
+      }
+      nk = nk2;
+      fin = f;
     }
     if (stripes == 0) FZ_STAMP(13);
     FZ_CLK(22);
-    cluster.sync();
-    FZ_CLK(23);
-    nk = s_status[0];
-    fin = s_status[1];
     ++stripes;
     c0 = presorted ? (c1 >= ps_end ? (int)s_end[ps_bin] : c1) : c1;
     if (presorted && ps_bin == cut_bin && c1 >= ps_end) break;
   }
   FZ_STAMP(7);
-  // ---- results (proposal.py:140-149) ----
+  // ---- the kept rows were written stripe by stripe; what is left: empty rows, counters ----
   if (rank == 0) {
     Ctrl* cb = g.ctrl + b;
     if (tid == 0) {
@@ -773,50 +866,14 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
     }
     const NmsOutputs& o = g.o;
     const size_t orow = (size_t)b * o.rows;
-    for (int j = tid; j < o.rows; j += blockDim.x) {
-      if (j < nk) {
-        const float4 a4 = __ldcg(kaux + j);
-        const int p = __float_as_int(a4.z);
-        int kpos = __float_as_int(a4.w);
-        if (o.rois) {
-          double bx[4];
-          exact_box(g, deltas, im_h, im_w, p, bx);
-          float* ro = o.rois + (orow + j) * 5;
-          ro[0] = (float)b;
-          ro[1] = (float)bx[0];
-          ro[2] = (float)bx[1];
-          ro[3] = (float)bx[2];
-          ro[4] = (float)bx[3];
-        }
-        if (o.scores) {  // the score sits at the flat (H,W,A) index of the FULL map (quirk Q1)
-          const int r = fast_div(p, dg.A, rcp_A), a = p - r * dg.A;
-          const int w2 = r % dg.W, h2 = r / dg.W;
-          o.scores[orow + j] = __ldg(fg + (size_t)a * hw + (size_t)h2 * dg.W + w2);
-        }
-        if (o.keep_orig) o.keep_orig[orow + j] = p;
-        if (o.keep_pos) {
-          if (kpos < 0) {  // bucket ordered in place: undo the tie-run reversal of nms.py:19 by looking at the neighbours
-            const int s = -1 - kpos;
-            const u32 key = (u32)(__ldcg(comp + s) >> 32);
-            const int bin = bin_of_key(key);
-            const int lo = (int)s_base[bin];
-            const int hi = lo + ((bin == s_plan[2] && (windows == 2 || c_w0 == cc)) ? s_plan[3] : (int)s_cnt[bin]);
-            int rs_ = s, re_ = s + 1;
-            while (rs_ > lo && (u32)(__ldcg(comp + rs_ - 1) >> 32) == key) --rs_;
-            while (re_ < hi && (u32)(__ldcg(comp + re_) >> 32) == key) ++re_;
-            kpos = rs_ + (re_ - 1 - s);
-          }
-          o.keep_pos[orow + j] = kpos;
-        }
-      } else {
-        if (o.rois) {
-          float* ro = o.rois + (orow + j) * 5;
-          ro[0] = ro[1] = ro[2] = ro[3] = ro[4] = 0.f;
-        }
-        if (o.scores) o.scores[orow + j] = 0.f;
-        if (o.keep_orig) o.keep_orig[orow + j] = -1;
-        if (o.keep_pos) o.keep_pos[orow + j] = -1;
+    for (int j = nk + tid; j < o.rows; j += blockDim.x) {
+      if (o.rois) {
+        float* ro = o.rois + (orow + j) * 5;
+        ro[0] = ro[1] = ro[2] = ro[3] = ro[4] = 0.f;
       }
+      if (o.scores) o.scores[orow + j] = 0.f;
+      if (o.keep_orig) o.keep_orig[orow + j] = -1;
+      if (o.keep_pos) o.keep_pos[orow + j] = -1;
     }
     if (tid == 0 && o.nkeep) {
       o.nkeep[b * 2] = nk;
@@ -840,9 +897,9 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
 }
 
 static inline size_t fused_smem_bytes(int items) {
-  const int items2 = (items + 1) / 2 * 2;
-  return (size_t)kWMax * (sizeof(float4) + sizeof(float2) + sizeof(u64) + 2 * sizeof(int)) + (16 + 16) * sizeof(u32) +
-         (size_t)kWMax * kMPitch * sizeof(u32) + (size_t)items2 * 1024 * sizeof(u32) + 64;
+  const int items2 = (items + 3) / 4 * 4;
+  return (size_t)kWMax * (sizeof(float4) + sizeof(float2) + sizeof(u64) + 3 * sizeof(int)) + (size_t)(kWMax / 2) * sizeof(float4) +
+         (16 + 32) * sizeof(u32) + (size_t)2 * kWMax * kMWords * sizeof(u32) + (size_t)items2 * 1024 * sizeof(u32) + 64;
 }
 
 }  // namespace fz
