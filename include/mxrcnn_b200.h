@@ -156,6 +156,17 @@ int mxr_proposal_wait_host(mxr_handle_t h, int slot, float* out_rois, float* out
 int mxr_proposal_pad(mxr_handle_t h, void* stream, int image, int rows_per_image, int nkeep, const int32_t* pad_rows,
                      int n_pad, float* out_rois, float* out_scores);
 
+/* Stage-level views of the proposal op for parity tests (mxr_decode_clip; rcnn/rpn/proposal.py:110-120).
+ * decode_clip: bbox_pred + clip_boxes + the min-size decision for EVERY anchor of the (cropped) map, device pointers,
+ * rows in the reference's order (h, w, a): out_boxes (B, A*hc*wc, 4) float64 -- the values the op's outputs are cast
+ * from -- and out_valid (B, A*hc*wc) int32 -- 1 where _filter_boxes (proposal.py:156-161) keeps the row, decided by
+ * the same screened test the fused kernel uses.
+ * counts: per image of the most recent proposal call [n_valid (= len(keep) of proposal.py:117), boxes entering NMS
+ * (proposal.py:123-127), boxes kept, NaN flag].  Synchronises. */
+int mxr_decode_clip(mxr_handle_t h, void* stream, const mxr_proposal_params* p, const float* bbox_pred, const float* im_info,
+                    const double* anchors, double* out_boxes, int32_t* out_valid);
+int mxr_proposal_counts(mxr_handle_t h, int max_images, int32_t* counts_out, int32_t* images_out);
+
 /* ---- A5  helper/processing/nms.py:4-38  nms(dets, thresh) ---------------------------- */
 /* dets dev (n,5) [x1,y1,x2,y2,score] f32 or f64 (arithmetic in that dtype, like numpy);
  * sorts by descending score (ties: higher index first), greedy-suppresses IoU > thresh.

@@ -70,6 +70,8 @@ SIGNATURES = {
     "mxr_proposal_stamps": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64), c_int_p]),
     "mxr_proposal_count_pairs": (ctypes.c_int, [_VP, ctypes.c_int]),
     "mxr_proposal_pairs_read": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), c_int_p]),
+    "mxr_decode_clip": (ctypes.c_int, [_VP, _VP, ctypes.POINTER(ProposalParams), _VP, _VP, c_double_p, _VP, _VP]),
+    "mxr_proposal_counts": (ctypes.c_int, [_VP, ctypes.c_int, c_int_p, c_int_p]),
     "mxr_generate_anchors": (ctypes.c_int, [ctypes.c_double, c_double_p, ctypes.c_int, c_double_p, ctypes.c_int,
                                             c_double_p]),
     "mxr_reserve_proposal": (ctypes.c_int, [_VP, ctypes.POINTER(ProposalParams)]),
@@ -198,6 +200,13 @@ class Handle(object):
         n = ctypes.c_int32(0)
         check(load().mxr_proposal_stamps(self._h, max_images, buf.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
                                          ctypes.byref(n)))
+        return buf[:n.value]
+
+    def proposal_counts(self, max_images=1024):
+        """(images, 4) int32 of the last proposal call: n_valid, boxes entering NMS, boxes kept, NaN flag."""
+        buf = np.zeros((max_images, 4), np.int32)
+        n = ctypes.c_int32(0)
+        check(load().mxr_proposal_counts(self._h, max_images, buf.ctypes.data_as(c_int_p), ctypes.byref(n)))
         return buf[:n.value]
 
     def count_pairs(self, on):

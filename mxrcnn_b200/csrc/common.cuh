@@ -108,6 +108,8 @@ struct Handle {
   int count_pairs;      // mxr_proposal_count_pairs(h, 1): the next fused calls count the IoU pairs they evaluate (un-timed runs)
   unsigned int* pair_ptr;  // device: per-image pair counters of the last such call
   int pair_images;
+  void* ctrl_ptr;       // device: control blocks of the last proposal call (mxr_proposal_counts)
+  int ctrl_images;
   unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
   int dbg_images;
   cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path

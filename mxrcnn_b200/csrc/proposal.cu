@@ -136,28 +136,15 @@ struct ProposalTier2 {
 };
 
 
-// Second-generation fused kernel (proposal_fused.cuh): ONE launch, any list length.  Returns MXR_ERR_UNSUPPORTED when an
-// image does not fit 16 CTAs x 12 keys x 1024 threads (the caller then takes the multi-kernel path).
-static const int MXR_ERR_UNSUPPORTED = -1000;
-int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layout& L, const ProposalGeom& pg,
-                  const AnchorTable& at, const float* cls_prob, const float* bbox_pred, const float* im_info, float* out_rois,
-                  float* out_scores, int32_t* out_keep, int32_t* out_anchor, int32_t* out_nkeep) {
-  static const int kNumSizes = 8;
-  static const int kSizes[kNumSizes] = {16, 14, 12, 10, 8, 6, 4, 2};
-  static const double kWaveCost[kNumSizes] = {0.883, 0.89, 0.925, 0.99, 1.0, 1.075, 1.35, 1.85};
-  if ((L.n_crop + 16 * 1024 - 1) / (16 * 1024) > 12) return MXR_ERR_UNSUPPORTED;
-  fz::FusedArgs* fa = new fz::FusedArgs();
-  struct Guard {
-    fz::FusedArgs* p;
-    ~Guard() { delete p; }
-  } guard{fa};
-  memset(fa, 0, sizeof(*fa));
+
+// The float32 anchor tables of the fused kernel's screens (proposal_fused.cuh: decode32_core) and their conversion errors.
+void fill_decode_tables(fz::FusedArgs* fa, const mxr_proposal_params* p, const ProposalGeom& pg, const AnchorTable& at, int A) {
   fa->pg = pg;
   fa->at = at;
   const double fs = p->feat_stride;
   fa->fs32 = (float)fs;
   fa->fs_err = (float)fabs(fs - (double)fa->fs32) * 1.0000002f;
-  for (int a = 0; a < L.A; ++a) {
+  for (int a = 0; a < A; ++a) {
     // bbox_transform.py:47-50 on the base anchor: width, height, centre (the shift w * feat_stride is added in the kernel)
     const double bw = at.a[a][2] - at.a[a][0] + 1.0, bh = at.a[a][3] - at.a[a][1] + 1.0;
     const double cx = at.a[a][0] + 0.5 * (bw - 1.0), cy = at.a[a][1] + 0.5 * (bh - 1.0);
@@ -174,10 +161,29 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
     // the kernel's bound covers through its 2^-23 |dx * bw| term as long as the conversion is within 2^-24 relative (it is)
     fa->at_err[a] = (float)err * 1.0000002f + (err > 0.0 ? 1e-30f : 0.0f);
   }
+  fa->min_size = p->min_size;
+}
+
+// Second-generation fused kernel (proposal_fused.cuh): ONE launch, any list length.  Returns MXR_ERR_UNSUPPORTED when an
+// image does not fit 16 CTAs x 12 keys x 1024 threads (the caller then takes the multi-kernel path).
+static const int MXR_ERR_UNSUPPORTED = -1000;
+int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layout& L, const ProposalGeom& pg,
+                  const AnchorTable& at, const float* cls_prob, const float* bbox_pred, const float* im_info, float* out_rois,
+                  float* out_scores, int32_t* out_keep, int32_t* out_anchor, int32_t* out_nkeep) {
+  static const int kNumSizes = 8;
+  static const int kSizes[kNumSizes] = {16, 14, 12, 10, 8, 6, 4, 2};
+  static const double kWaveCost[kNumSizes] = {0.883, 0.89, 0.925, 0.99, 1.0, 1.075, 1.35, 1.85};
+  if ((L.n_crop + 16 * 1024 - 1) / (16 * 1024) > 12) return MXR_ERR_UNSUPPORTED;
+  fz::FusedArgs* fa = new fz::FusedArgs();
+  struct Guard {
+    fz::FusedArgs* p;
+    ~Guard() { delete p; }
+  } guard{fa};
+  memset(fa, 0, sizeof(*fa));
+  fill_decode_tables(fa, p, pg, at, L.A);
   fa->cls_prob = cls_prob;
   fa->bbox_pred = bbox_pred;
   fa->im_info = im_info;
-  fa->min_size = p->min_size;
   fa->pre_nms = p->pre_nms_top_n;
   fa->max_keep = p->post_nms_top_n > 0 ? L.keep_cap : 0;
   // stripe widths: the first stripe should settle a small quota on its own (the 300th keep sits near sorted position
@@ -210,6 +216,8 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
   fa->o.rows = L.out_rows;
   fa->o.row_offsets = nullptr;
   fa->ctrl = L.ctrl;
+  h->ctrl_ptr = L.ctrl;
+  h->ctrl_images = L.B;
   fa->dbg = h->prof_on ? L.dbg : nullptr;
   fa->clk = h->prof_on ? L.dbg + (size_t)L.B * 16 : nullptr;
   h->dbg_ptr = fa->dbg;
@@ -642,6 +650,67 @@ int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, con
   MXR_REQUIRE(out_rois && out_nkeep, MXR_ERR_INVALID, "mxr_proposal_forward_host: NULL array argument");
   MXR_TRY(mxr_proposal_submit_host(hh, 0, p, cls_prob, bbox_pred, im_info, anchors, out_capacity));
   return mxr_proposal_wait_host(hh, 0, out_rois, out_scores, out_keep, out_anchor_index, out_nkeep);
+}
+
+int mxr_decode_clip(mxr_handle_t hh, void* stream, const mxr_proposal_params* p, const float* bbox_pred, const float* im_info,
+                    const double* anchors, double* out_boxes, int32_t* out_valid) {
+  MXR_REQUIRE(hh != nullptr && bbox_pred && im_info && anchors && out_boxes && out_valid, MXR_ERR_INVALID,
+              "mxr_decode_clip: NULL argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  Layout L;
+  MXR_TRY(make_layout(p, 1, false, nullptr, &L));
+  AnchorTable at;
+  memset(&at, 0, sizeof(at));
+  memcpy(at.a, anchors, sizeof(double) * 4 * L.A);
+  ProposalGeom pg;
+  memset(&pg, 0, sizeof(pg));
+  pg.g.A = L.A;
+  pg.g.H = L.H;
+  pg.g.W = L.W;
+  pg.g.hc = L.hc;
+  pg.g.wc = L.wc;
+  pg.g.fs = p->feat_stride;
+  pg.n_crop = L.n_crop;
+  pg.n_full = L.n_full;
+  pg.cropped = L.cropped;
+  fz::FusedArgs* fa = new fz::FusedArgs();
+  memset(fa, 0, sizeof(*fa));
+  fill_decode_tables(fa, p, pg, at, L.A);
+  fa->bbox_pred = bbox_pred;
+  fa->im_info = im_info;
+  dim3 grid((L.n_crop + 255) / 256, L.B);
+  fz::decode_stage_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*fa, out_boxes, out_valid);
+  delete fa;
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
+int mxr_proposal_counts(mxr_handle_t hh, int max_images, int32_t* counts_out, int32_t* images_out) {
+  MXR_REQUIRE(hh != nullptr && counts_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
+              "mxr_proposal_counts: bad argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_CUDA(cudaSetDevice(h->device));
+  *images_out = 0;
+  if (!h->ctrl_ptr || h->ctrl_images <= 0) return MXR_OK;
+  MXR_CUDA(cudaDeviceSynchronize());
+  const int n = h->ctrl_images < max_images ? h->ctrl_images : max_images;
+  Ctrl* tmp = new Ctrl[n];
+  cudaError_t e = cudaMemcpy(tmp, h->ctrl_ptr, (size_t)n * sizeof(Ctrl), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) {
+    delete[] tmp;
+    set_error("mxr_proposal_counts: %s", cudaGetErrorString(e));
+    return MXR_ERR_CUDA;
+  }
+  for (int b = 0; b < n; ++b) {
+    counts_out[b * 4] = tmp[b].n_valid;
+    counts_out[b * 4 + 1] = tmp[b].n;
+    counts_out[b * 4 + 2] = tmp[b].nkept;
+    counts_out[b * 4 + 3] = tmp[b].nan_flag;
+  }
+  delete[] tmp;
+  *images_out = n;
+  return MXR_OK;
 }
 
 int mxr_proposal_pad(mxr_handle_t hh, void* stream, int image, int rows_per_image, int nkeep, const int32_t* pad_rows,

@@ -210,6 +210,49 @@ __device__ __noinline__ bool exact_pair(const FusedArgs& g, const float* __restr
                              bc[3], box_area<double>(bc[0], bc[1], bc[2], bc[3]), g.thr);
 }
 
+// Min-size filter (proposal.py:113-120, 156-161) on the float32 image of the box; the reference's float64 arithmetic
+// decides only when a side is within the error bound of the threshold (or nothing is finite).  Same decision as
+// passes_min_size(decode_clip_values(...)) for every input.
+__device__ __forceinline__ bool min_size_screened(const FusedArgs& g, float dx, float dy, float dw, float dh, int h, int w,
+                                                  int a, float lim_x, float lim_y, float ms32, float im_h, float im_w,
+                                                  float im_s) {
+  const Dec32 d = decode32_core(g, dx, dy, dw, dh, h, w, a, lim_x, lim_y);
+  const float ws = (d.x2 - d.x1) + 1.0f, hs = (d.y2 - d.y1) + 1.0f;
+  const float m = 2.0f * d.e + 2.3841858e-07f * (fmaxf(ws, hs) + 1.0f);  // 2e + 2^-22 (side + 1)
+  const float lo = fminf(ws, hs) - ms32;
+  bool valid = lo > m;
+  if (!valid && !(lo < -m)) valid = exact_min_size(g, dx, dy, dw, dh, h, w, a, im_h, im_w, im_s);
+  return valid;
+}
+
+// Stage entry (mxr_decode_clip): what the fused kernel decides and decodes, for EVERY anchor of the cropped map, in the
+// reference's row order p = (h * wc + w) * A + a (proposal.py:88-120).  boxes: the float64 decode the kernel's outputs
+// are cast from; valid: the min-size decision of the screened filter above.  grid (ceil(n_crop / 256), B).
+__global__ void __launch_bounds__(256) decode_stage_kernel(const __grid_constant__ FusedArgs g, double* __restrict__ boxes,
+                                                           int* __restrict__ valid_out) {
+  const ProposalGeom& pg = g.pg;
+  const DecodeGeom& dg = pg.g;
+  const int b = blockIdx.y;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= pg.n_crop) return;
+  const size_t hw = (size_t)dg.H * dg.W;
+  const float* deltas = g.bbox_pred + (size_t)b * 4 * dg.A * hw;
+  const float im_h = __ldg(g.im_info + b * 3), im_w = __ldg(g.im_info + b * 3 + 1), im_s = __ldg(g.im_info + b * 3 + 2);
+  const float lim_x = __fsub_rn(im_w, 1.0f), lim_y = __fsub_rn(im_h, 1.0f);
+  const float ms32 = __fmul_rn(g.min_size, im_s);
+  const int a = p % dg.A, r = p / dg.A, h = r / dg.wc, w = r - h * dg.wc;
+  const float* d = deltas + ((size_t)a * 4) * hw + (size_t)h * dg.W + w;
+  const float dx = __ldg(d), dy = __ldg(d + hw), dw = __ldg(d + 2 * hw), dh = __ldg(d + 3 * hw);
+  double bx[4];
+  decode_clip_values(g.at, dg, dx, dy, dw, dh, h, w, a, im_h, im_w, bx);
+  double* o = boxes + ((size_t)b * pg.n_crop + p) * 4;
+  o[0] = bx[0];
+  o[1] = bx[1];
+  o[2] = bx[2];
+  o[3] = bx[3];
+  valid_out[(size_t)b * pg.n_crop + p] = min_size_screened(g, dx, dy, dw, dh, h, w, a, lim_x, lim_y, ms32, im_h, im_w, im_s) ? 1 : 0;
+}
+
 // A bucket with more candidates than a stripe is wide (scores crowded into one bin) cannot be ranked by counting while
 // it is staged: the leader CTA orders it in place with a sort in global memory -- first by the selection order (score
 // desc, row desc: proposal.py:123-125 with the documented tie rule) to apply the pre-NMS cut to the first r, then by the
@@ -336,14 +379,8 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       for (int j = 0; j < FZ_P1_GROUP; ++j) {
         u32 key = 0;
         if (ia[j] >= 0) {
-          // min-size filter (proposal.py:113-120, 156-161) on the float32 image of the box; the reference's float64
-          // arithmetic decides only when a side is within the error bound of the threshold (or nothing is finite)
-          const Dec32 d = decode32_core(g, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], lim_x, lim_y);
-          const float ws = (d.x2 - d.x1) + 1.0f, hs = (d.y2 - d.y1) + 1.0f;
-          const float m = 2.0f * d.e + 2.3841858e-07f * (fmaxf(ws, hs) + 1.0f);  // 2e + 2^-22 (side + 1)
-          const float lo = fminf(ws, hs) - ms32;
-          bool valid = lo > m;
-          if (!valid && !(lo < -m)) valid = exact_min_size(g, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], im_h, im_w, im_s);
+          const bool valid = min_size_screened(g, dx[j], dy[j], dw[j], dh[j], ih[j], iw[j], ia[j], lim_x, lim_y, ms32, im_h,
+                                               im_w, im_s);
           // the clip drops NaNs, so the reference's NaN check (proposal.py:58-62) looks at the raw values
           nanflag |= (sc[j] != sc[j]) || (dx[j] != dx[j]) || (dy[j] != dy[j]) || (dw[j] != dw[j]) || (dh[j] != dh[j]);
           key = valid ? score_key32(sc[j]) : 0u;
