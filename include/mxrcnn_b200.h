@@ -148,6 +148,12 @@ int mxr_proposal_forward_host(mxr_handle_t h, const mxr_proposal_params* p, cons
  * mxr_reserve_proposal first: the workspace cannot grow while the other slot is in flight. */
 int mxr_proposal_submit_host(mxr_handle_t h, int slot, const mxr_proposal_params* p, const float* cls_prob,
                              const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity);
+/* The same with the inputs packed by the caller into ONE host block, so that they cross the bus in one copy:
+ * [foreground scores (B, A, H, W)] [bbox deltas (B, 4A, H, W)] [im_info (B, 3)], float32, contiguous -- the arrays
+ * of proposal.py:57-63 (cls_prob[:, A:], bbox_pred, im_info) laid end to end.  Results are fetched with
+ * mxr_proposal_wait_host as usual. */
+int mxr_proposal_submit_host_packed(mxr_handle_t h, int slot, const mxr_proposal_params* p, const float* packed,
+                                    const double* anchors, int out_capacity);
 int mxr_proposal_wait_host(mxr_handle_t h, int slot, float* out_rois, float* out_scores, int32_t* out_keep,
                            int32_t* out_anchor_index, int32_t* out_nkeep);
 

@@ -81,6 +81,8 @@ SIGNATURES = {
                                                  ctypes.c_int, _VP, _VP, _VP, _VP, _VP]),
     "mxr_proposal_submit_host": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ProposalParams), _VP, _VP, _VP,
                                                 c_double_p, ctypes.c_int]),
+    "mxr_proposal_submit_host_packed": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ProposalParams), _VP, c_double_p,
+                                                       ctypes.c_int]),
     "mxr_proposal_wait_host": (ctypes.c_int, [_VP, ctypes.c_int, _VP, _VP, _VP, _VP, _VP]),
     "mxr_proposal_pad": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_int_p, ctypes.c_int,
                                         _VP, _VP]),

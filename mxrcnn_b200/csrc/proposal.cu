@@ -55,6 +55,7 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
               MXR_ERR_INVALID, "proposal: bad shape B=%d A=%d H=%d W=%d (A must be 1..64)", p->batch, p->num_anchors,
               p->height, p->width);
   MXR_REQUIRE(p->feat_stride > 0, MXR_ERR_INVALID, "proposal: feat_stride must be > 0");
+  MXR_REQUIRE(p->batch <= 65535, MXR_ERR_LIMIT, "proposal: at most 65535 images per call (got %d)", p->batch);
   L->B = p->batch;
   L->A = p->num_anchors;
   L->H = p->height;
@@ -103,9 +104,10 @@ int make_layout(const mxr_proposal_params* p, int out_capacity, bool host_io, ch
   L->pair_count = c.take<u32>((size_t)L->B * 2);
   if (host_io) {
     const size_t hw = (size_t)L->H * L->W;
-    L->d_cls = c.take<float>((size_t)L->B * L->A * hw);  // foreground half only
-    L->d_box = c.take<float>((size_t)L->B * 4 * L->A * hw);
-    L->d_info = c.take<float>((size_t)L->B * 3);
+    // ONE block -- foreground scores | deltas | im_info -- so that a caller-packed host buffer arrives in one copy
+    L->d_cls = c.take<float>((size_t)L->B * L->A * hw + (size_t)L->B * 4 * L->A * hw + (size_t)L->B * 3);
+    L->d_box = L->d_cls + (size_t)L->B * L->A * hw;
+    L->d_info = L->d_box + (size_t)L->B * 4 * L->A * hw;
     const size_t rows = (size_t)L->B * L->out_rows;
     size_t o = 0;
     o += align_up(rows * 5 * sizeof(float), 256);
@@ -271,13 +273,23 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
   MXR_REQUIRE(csize != 0, MXR_ERR_CUDA, "proposal: no cluster size of the fused kernel fits this device");
   void (*kern)(const fz::FusedArgs) = fz::proposal_fused_kernel;
   fa->items = items;
+  fa->chunk = (L.n_crop + csize - 1) / csize;
+  fa->hwc = L.hc * L.wc;
+  fa->hw32 = L.H * L.W;
+  fa->rcp_hwc = 1.0f / (float)fa->hwc;
+  fa->rcp_wc = 1.0f / (float)L.wc;
+  fa->rcp_A = 1.0f / (float)L.A;
+  fa->a_step = 1024 / fa->hwc;
+  fa->r_step = 1024 % fa->hwc;
+  fa->h_step = fa->r_step / L.wc;
+  fa->w_step = fa->r_step % L.wc;
   {
     const char* nr = getenv("MXRCNN_B200_NULL");
     fa->null_run = (nr && nr[0] == '1') ? 1 : 0;
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(L.B * csize);
+  cfg.gridDim = dim3(csize, L.B);  // blockIdx.y = image: no division in the kernel
   cfg.blockDim = dim3(1024);
   cfg.dynamicSmemBytes = fz::fused_smem_bytes(items <= 4 ? 4 : 12);
   cfg.stream = s;
@@ -568,11 +580,13 @@ struct HostSlots {
   int busy[2];
 };
 
-int mxr_proposal_submit_host(mxr_handle_t hh, int slot, const mxr_proposal_params* p, const float* cls_prob,
-                             const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity) {
+static int submit_host_impl(mxr_handle_t hh, int slot, const mxr_proposal_params* p, const float* cls_prob,
+                            const float* bbox_pred, const float* im_info, const float* packed, const double* anchors,
+                            int out_capacity) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_proposal_submit_host: NULL handle");
   MXR_REQUIRE(slot == 0 || slot == 1, MXR_ERR_INVALID, "mxr_proposal_submit_host: slot must be 0 or 1");
-  MXR_REQUIRE(cls_prob && bbox_pred && im_info && anchors, MXR_ERR_INVALID, "mxr_proposal_submit_host: NULL array argument");
+  MXR_REQUIRE(((cls_prob && bbox_pred && im_info) || packed) && anchors, MXR_ERR_INVALID,
+              "mxr_proposal_submit_host: NULL array argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
   MXR_CUDA(cudaSetDevice(h->device));
   if (!h->prop_state) {
@@ -596,12 +610,17 @@ int mxr_proposal_submit_host(mxr_handle_t hh, int slot, const mxr_proposal_param
   MXR_TRY(make_layout(p, out_capacity, true, h->d_ws + (size_t)slot * (h->d_bytes / 2 / 256 * 256), &L));
   cudaStream_t s = slot ? h->stream2 : h->stream;
   const size_t hw = (size_t)L.H * L.W;
-  // only the foreground half of cls_prob crosses the bus (proposal.py:57)
   const size_t fg_bytes = (size_t)L.A * hw * sizeof(float);
-  MXR_CUDA(cudaMemcpy2DAsync(L.d_cls, fg_bytes, cls_prob + (size_t)L.A * hw, 2 * fg_bytes, fg_bytes, L.B,
+  if (packed) {  // foreground scores | deltas | im_info, as the device block is laid out: one copy
+    MXR_CUDA(cudaMemcpyAsync(L.d_cls, packed, (size_t)L.B * 5 * fg_bytes + (size_t)L.B * 3 * sizeof(float),
                              cudaMemcpyHostToDevice, s));
-  MXR_CUDA(cudaMemcpyAsync(L.d_box, bbox_pred, (size_t)L.B * 4 * fg_bytes, cudaMemcpyHostToDevice, s));
-  MXR_CUDA(cudaMemcpyAsync(L.d_info, im_info, (size_t)L.B * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
+  } else {
+    // only the foreground half of cls_prob crosses the bus (proposal.py:57)
+    MXR_CUDA(cudaMemcpy2DAsync(L.d_cls, fg_bytes, cls_prob + (size_t)L.A * hw, 2 * fg_bytes, fg_bytes, L.B,
+                               cudaMemcpyHostToDevice, s));
+    MXR_CUDA(cudaMemcpyAsync(L.d_box, bbox_pred, (size_t)L.B * 4 * fg_bytes, cudaMemcpyHostToDevice, s));
+    MXR_CUDA(cudaMemcpyAsync(L.d_info, im_info, (size_t)L.B * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
+  }
   float* d_rois = reinterpret_cast<float*>(L.d_out);
   float* d_scores = reinterpret_cast<float*>(L.d_out + L.off_scores);
   int* d_keep = reinterpret_cast<int*>(L.d_out + L.off_keep);
@@ -613,6 +632,18 @@ int mxr_proposal_submit_host(mxr_handle_t hh, int slot, const mxr_proposal_param
                            cudaMemcpyDeviceToHost, s));
   hs->busy[slot] = 1;
   return MXR_OK;
+}
+
+int mxr_proposal_submit_host(mxr_handle_t hh, int slot, const mxr_proposal_params* p, const float* cls_prob,
+                             const float* bbox_pred, const float* im_info, const double* anchors, int out_capacity) {
+  MXR_REQUIRE(cls_prob && bbox_pred && im_info, MXR_ERR_INVALID, "mxr_proposal_submit_host: NULL array argument");
+  return submit_host_impl(hh, slot, p, cls_prob, bbox_pred, im_info, nullptr, anchors, out_capacity);
+}
+
+int mxr_proposal_submit_host_packed(mxr_handle_t hh, int slot, const mxr_proposal_params* p, const float* packed,
+                                    const double* anchors, int out_capacity) {
+  MXR_REQUIRE(packed != nullptr, MXR_ERR_INVALID, "mxr_proposal_submit_host_packed: NULL array argument");
+  return submit_host_impl(hh, slot, p, nullptr, nullptr, nullptr, packed, anchors, out_capacity);
 }
 
 int mxr_proposal_wait_host(mxr_handle_t hh, int slot, float* out_rois, float* out_scores, int32_t* out_keep,

@@ -48,6 +48,12 @@ struct FusedArgs {
   int max_keep;      // > 0: post_nms_top_n
   int items;         // score keys per thread: ceil(n_crop / (cluster size * 1024))
   int null_run;      // MXRCNN_B200_NULL=1 (measurement only): leave right after the dependency wait
+  // launch constants, computed once on the host instead of by every thread (integer divisions, reciprocals)
+  int chunk;         // anchors per CTA: ceil(n_crop / cluster size)
+  int hwc, hw32;     // hc * wc, H * W
+  float rcp_hwc, rcp_wc, rcp_A;
+  int a_step, r_step, h_step, w_step;  // a thread's next anchor is 1024 further: 1024 = a_step * hwc + r_step,
+                                       // r_step = h_step * wc + w_step
   int first_stripe;  // width of the first stripe (multiple of 32, <= kWMax)
   int next_stripe;   // width of the later stripes
   int window0;       // candidates the first window should hold
@@ -83,6 +89,12 @@ __device__ __forceinline__ u64 global_ns() {
 __device__ __forceinline__ int bin_of_key(u32 key) {
   const u32 bits = (key & 0x80000000u) ? (key & 0x7fffffffu) : ~key;  // inverse of score_key32
   const int v = (int)(__uint_as_float(bits) * (float)kBins);           // saturating conversion
+  return v < 0 ? 0 : (v > kBins - 1 ? kBins - 1 : v);
+}
+
+// The same bin from the score itself (bin_of_key(score_key32(s)) == bin_of_score(s): the key is a bijection of s + 0).
+__device__ __forceinline__ int bin_of_score(float s) {
+  const int v = (int)(s * (float)kBins);
   return v < 0 ? 0 : (v > kBins - 1 ? kBins - 1 : v);
 }
 
@@ -281,7 +293,7 @@ __device__ __forceinline__ int first_bin_ending_by(const u32* s_end, int lo_mat,
   return 32 * g1 + __ffs(m2) - 1;
 }
 
-// grid B * csize CTAs, cluster (csize,1,1), block 1024.  g.items keys per thread (n_crop <= csize * items * 1024).
+// grid (csize, B), cluster (csize,1,1), block 1024.  g.items keys per thread (n_crop <= csize * items * 1024).
 __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_constant__ FusedArgs g) {
   namespace cgx = cooperative_groups;
   extern __shared__ __align__(16) unsigned char dyn_smem[];
@@ -301,7 +313,7 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   cgx::cluster_group cluster = cgx::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int csize = (int)cluster.num_blocks();
-  const int b = blockIdx.x / csize;
+  const int b = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const ProposalGeom& pg = g.pg;
   const DecodeGeom& dg = pg.g;
@@ -329,20 +341,30 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   FZ_STAMP(1);
 
   // ---- P1: decode + clip + min-size filter (proposal.py:77-120); score keys go to shared memory ----
-  const int hwc = dg.hc * dg.wc;
-  const size_t hw = (size_t)dg.H * dg.W;
+  const int hwc = g.hwc;
+  const int hw32 = g.hw32;
+  const size_t hw = (size_t)hw32;
   const float* fg = g.cls_prob + (size_t)b * pg.cls_img_stride + pg.cls_fg_offset;
   const float* deltas = g.bbox_pred + (size_t)b * 4 * dg.A * hw;
   const float im_h = __ldg(g.im_info + b * 3), im_w = __ldg(g.im_info + b * 3 + 1), im_s = __ldg(g.im_info + b * 3 + 2);
-  const int chunk = (pg.n_crop + csize - 1) / csize;
+  const int chunk = g.chunk;
   const int q_begin = rank * chunk;
   const int q_end = min(q_begin + chunk, pg.n_crop);
-  const float rcp_hwc = 1.0f / (float)hwc, rcp_wc = 1.0f / (float)dg.wc, rcp_A = 1.0f / (float)dg.A;
+  const float rcp_hwc = g.rcp_hwc, rcp_wc = g.rcp_wc, rcp_A = g.rcp_A;
   const float lim_x = __fsub_rn(im_w, 1.0f), lim_y = __fsub_rn(im_h, 1.0f);
   const float ms32 = __fmul_rn(g.min_size, im_s);  // proposal.py:117: an f32 product under numpy >= 2 (NEP 50)
   const int items = g.items;
   {
     bool nanflag = false;
+    // this thread's anchors are q_begin + tid + 1024 i: (a, h, w) of the first by division, of the others by stepping
+    int qa, qr, qh, qw;
+    {
+      const int q0 = q_begin + tid;
+      qa = fast_div(q0, hwc, rcp_hwc);
+      qr = q0 - qa * hwc;
+      qh = fast_div(qr, dg.wc, rcp_wc);
+      qw = qr - qh * dg.wc;
+    }
     // Four anchors per round: first ALL twenty loads (independent of each other: one DRAM round trip for an image of up
     // to four keys per thread), then the arithmetic.
 #pragma unroll 1
@@ -353,26 +375,37 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       for (int j = 0; j < FZ_P1_GROUP; ++j) {
         const int q = q_begin + tid + (i0 + j) * 1024;
         ia[j] = -1;
-        ih[j] = iw[j] = 0;
+        ih[j] = qh;
+        iw[j] = qw;
         dx[j] = dy[j] = dw[j] = dh[j] = sc[j] = 0.0f;
         if (q < q_end) {
-          const int a = fast_div(q, hwc, rcp_hwc), r = q - a * hwc;
-          const int h = fast_div(r, dg.wc, rcp_wc), w = r - h * dg.wc;
-          ia[j] = a;
-          ih[j] = h;
-          iw[j] = w;
-          const float* d = deltas + ((size_t)a * 4) * hw + (size_t)h * dg.W + w;
-          dx[j] = __ldg(d);
-          dy[j] = __ldg(d + hw);
-          dw[j] = __ldg(d + 2 * hw);
-          dh[j] = __ldg(d + 3 * hw);
+          ia[j] = qa;
+          const int od = qa * 4 * hw32 + qh * dg.W + qw;
+          dx[j] = __ldg(deltas + od);
+          dy[j] = __ldg(deltas + od + hw32);
+          dw[j] = __ldg(deltas + od + 2 * hw32);
+          dh[j] = __ldg(deltas + od + 3 * hw32);
           if (!pg.cropped) {
-            sc[j] = __ldg(fg + (size_t)a * hw + (size_t)h * dg.W + w);
+            sc[j] = __ldg(fg + q);  // q = a * H * W + h * W + w on an uncropped map
           } else {  // quirk Q1: scores are read at the flat (H,W,A) index of the UNCROPPED map
-            const int p = r * dg.A + a;
+            const int p = qr * dg.A + qa;
             const int a2 = p % dg.A, w2 = (p / dg.A) % dg.W, h2 = p / (dg.A * dg.W);
             sc[j] = __ldg(fg + (size_t)a2 * hw + (size_t)h2 * dg.W + w2);
           }
+        }
+        // step to this thread's next anchor (1024 further)
+        qa += g.a_step;
+        qr += g.r_step;
+        qh += g.h_step;
+        qw += g.w_step;
+        if (qw >= dg.wc) {
+          qw -= dg.wc;
+          ++qh;
+        }
+        if (qr >= hwc) {
+          qr -= hwc;
+          qh -= dg.hc;
+          ++qa;
         }
       }
 #pragma unroll
@@ -383,14 +416,16 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
                                                im_w, im_s);
           // the clip drops NaNs, so the reference's NaN check (proposal.py:58-62) looks at the raw values
           nanflag |= (sc[j] != sc[j]) || (dx[j] != dx[j]) || (dy[j] != dy[j]) || (dw[j] != dw[j]) || (dh[j] != dh[j]);
-          key = valid ? score_key32(sc[j]) : 0u;
+          if (valid) {
+            key = score_key32(sc[j]);
+            atomicAdd(&s_bins[bin_of_score(sc[j])], 1u);
+          }
         }
         s_keys[(i0 + j) * 1024 + tid] = key;
-        if (key != 0u) atomicAdd(&s_bins[bin_of_key(key)], 1u);
       }
     }
     if (pg.cropped) {  // proposal.py:58-62 checks the whole arrays, cropped or not
-      const int fchunk = (pg.n_full + csize - 1) / csize;
+      const int fchunk = (pg.n_full + csize - 1) / csize;  // (cropped maps only)
       for (int q = rank * fchunk + tid; q < min((rank + 1) * fchunk, pg.n_full); q += 1024) {
         const float v0 = __ldg(fg + q), v1 = __ldg(deltas + q), v2 = __ldg(deltas + q + pg.n_full);
         const float v3 = __ldg(deltas + q + 2 * (size_t)pg.n_full), v4 = __ldg(deltas + q + 3 * (size_t)pg.n_full);
@@ -526,22 +561,48 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
       }
       __syncthreads();
       // bin(s) >= bot  <=>  s >= bot / 1024 (the bin function is monotone and bot / 1024 is exact), so most keys are
-      // turned away by one comparison
+      // turned away by one comparison.  The few that pass are first compacted per warp (a warp-private queue in the
+      // staging area, free at this point), so that the slot arithmetic runs on full warps of candidates instead of on
+      // every warp that happens to hold one.
       const u32 key_bot = bot == 0 ? 1u : score_key32((float)bot * (1.0f / (float)kBins));
-#pragma unroll 1
-      for (int i = 0; i < items; ++i) {
-        const u32 key = s_keys[i * 1024 + tid];
-        if (key >= key_bot) {
+      u64* wq = reinterpret_cast<u64*>(dyn_smem) + warp * 64;  // [64] (key << 32 | item index), 16 KB for 32 warps
+      int cnt = 0;
+      auto place = [&](int n) {  // lanes < n take queue entries 0 .. n-1
+        if (lane < n) {
+          const u64 e = wq[lane];
+          const u32 key = (u32)(e >> 32);
           const int bin = bin_of_key(key);
-          if (bin >= bot && bin <= top && s_cnt[bin] != 0u) {
+          if (bin <= top && s_cnt[bin] != 0u) {
             const u32 slot = s_own[bin] + atomicAdd(&s_bins[bin], 1u);
-            const int q = q_begin + tid + i * 1024;
+            const int q = q_begin + tid - lane + (int)(u32)e;  // (u32)e = item * 1024 + lane of the key's owner
             const int a = fast_div(q, hwc, rcp_hwc);
             const u32 p = (u32)((q - a * hwc) * dg.A + a);  // row index of the reference: (h * wc + w) * A + a
             comp[slot] = ((u64)key << 32) | (u32)(~p);
           }
         }
+      };
+#pragma unroll 1
+      for (int i = 0; i < items; ++i) {
+        const u32 key = s_keys[i * 1024 + tid];
+        const bool sel = key >= key_bot;
+        const u32 m = __ballot_sync(0xffffffffu, sel);
+        if (m) {
+          if (sel) wq[cnt + __popc(m & ((1u << lane) - 1u))] = ((u64)key << 32) | (u32)(i * 1024 + lane);
+          cnt += __popc(m);
+          __syncwarp();
+          if (cnt >= 32) {
+            place(32);
+            __syncwarp();
+            const u64 e = lane < cnt - 32 ? wq[32 + lane] : 0ull;  // move the rest to the front
+            __syncwarp();
+            if (lane < cnt - 32) wq[lane] = e;
+            cnt -= 32;
+            __syncwarp();
+          }
+        }
       }
+      place(cnt);
+      __syncthreads();  // the queues alias the stripe staging area
       lo_mat = (c_lo == cc) ? s_plan[2] : bot;
       ++windows;
       cluster.sync();  // the window's composites are visible to every CTA of the cluster
