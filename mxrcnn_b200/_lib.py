@@ -256,6 +256,34 @@ def default_handle(device=None):
     return cache[device]
 
 
+def device_id_of(x):
+    """CUDA device ordinal a device array lives on."""
+    if hasattr(x, "is_cuda"):
+        idx = x.device.index
+        if idx is None:
+            import torch
+            idx = torch.cuda.current_device()
+        return int(idx)
+    if hasattr(x, "__dlpack_device__"):
+        return int(x.__dlpack_device__()[1])
+    return 0
+
+
+def handle_for(handle, *arrays):
+    """The handle a helper should use: the caller's (checked against the device the arrays live on), else the
+    calling thread's default handle of THAT device -- never a handle of another GPU than the data's."""
+    dev = None
+    for a in arrays:
+        if a is not None and is_device_array(a):
+            dev = device_id_of(a)
+            break
+    if handle is not None:
+        if dev is not None and handle.device != dev:
+            raise ValueError("handle of device %d used with arrays on device %d" % (handle.device, dev))
+        return handle
+    return default_handle(dev)
+
+
 # ---------------------------------------------------------------------------------------
 # array plumbing
 # ---------------------------------------------------------------------------------------

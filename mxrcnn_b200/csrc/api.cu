@@ -51,6 +51,29 @@ int ensure_pinned_ws(Handle* h, size_t bytes) {
   return MXR_OK;
 }
 
+int ws_order(Handle* h, cudaStream_t s) {
+  const bool s_private = (s == h->stream) || (h->stream2 && s == h->stream2);
+  if (!h->ws_used) {
+    h->ws_used = 1;
+  } else if (h->ws_last_private && s_private) {
+    // the handle's own streams: the two slots of the pipelined host path use disjoint halves, everything else runs on
+    // h->stream in order
+  } else if (!h->ws_last_private && h->ws_last == s) {
+    // same caller stream as last time: stream order
+  } else if (h->ws_last_private) {
+    if (cudaEventRecord(h->ev, h->stream) == cudaSuccess) cudaStreamWaitEvent(s, h->ev, 0);
+    if (h->stream2 && cudaEventRecord(h->ev2, h->stream2) == cudaSuccess) cudaStreamWaitEvent(s, h->ev2, 0);
+    (void)cudaGetLastError();
+  } else {
+    // the previous caller stream may have been destroyed since (its work then completes on its own): errors are dropped
+    if (cudaEventRecord(h->ev, h->ws_last) == cudaSuccess) cudaStreamWaitEvent(s, h->ev, 0);
+    (void)cudaGetLastError();
+  }
+  h->ws_last = s;
+  h->ws_last_private = s_private ? 1 : 0;
+  return MXR_OK;
+}
+
 // Kernel attributes and the occupancy figures derived from them, per device, shared by all handles.
 static const int kMaxDevices = 64;
 struct DeviceCache {
@@ -96,6 +119,7 @@ int mxr_create(int device, mxr_handle_t* out) {
   h->cluster_cap = g_dev_cache[device].cluster_cap;
   MXR_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   MXR_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
+  MXR_CUDA(cudaEventCreateWithFlags(&h->ev2, cudaEventDisableTiming));
   const char* nc = getenv("MXRCNN_B200_NO_CLUSTER");
   h->no_cluster = (nc && nc[0] == '1') ? 1 : 0;
   const char* c8 = getenv("MXRCNN_B200_CLUSTER8");
@@ -124,6 +148,7 @@ int mxr_destroy(mxr_handle_t hh) {
   if (h->prop_state) free(h->prop_state);
   if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->ev) cudaEventDestroy(h->ev);
+  if (h->ev2) cudaEventDestroy(h->ev2);
   if (h->prof) {
     for (int i = 0; i < h->prof_cap; ++i) {
       cudaEventDestroy(h->prof[i].a);
@@ -141,7 +166,7 @@ size_t mxr_workspace_bytes(mxr_handle_t hh) { return hh ? reinterpret_cast<Handl
 int mxr_profile_enable(mxr_handle_t hh, int on) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_profile_enable: NULL handle");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   if (on && !h->prof) {
     h->prof_cap = 1 << 15;
     h->prof = new ProfRec[h->prof_cap];
@@ -158,7 +183,7 @@ int mxr_profile_enable(mxr_handle_t hh, int on) {
 int mxr_profile_read(mxr_handle_t hh, int max_stages, double* total_ms, int32_t* counts) {
   MXR_REQUIRE(hh != nullptr && total_ms && counts && max_stages >= 1, MXR_ERR_INVALID, "mxr_profile_read: bad argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   MXR_CUDA(cudaDeviceSynchronize());
   for (int i = 0; i < max_stages; ++i) {
     total_ms[i] = 0;
@@ -191,7 +216,7 @@ int mxr_proposal_phase_times(mxr_handle_t hh, int max_images, double* us_out, in
   MXR_REQUIRE(hh != nullptr && us_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
               "mxr_proposal_phase_times: bad argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   *images_out = 0;
   if (!h->dbg_ptr || h->dbg_images <= 0) return MXR_OK;
   MXR_CUDA(cudaDeviceSynchronize());
@@ -216,7 +241,7 @@ int mxr_proposal_stamps(mxr_handle_t hh, int max_images, uint64_t* ns_out, int32
   MXR_REQUIRE(hh != nullptr && ns_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
               "mxr_proposal_stamps: bad argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   *images_out = 0;
   if (!h->dbg_ptr || h->dbg_images <= 0) return MXR_OK;
   MXR_CUDA(cudaDeviceSynchronize());
@@ -248,7 +273,7 @@ int mxr_proposal_pairs_read(mxr_handle_t hh, int max_images, uint32_t* pairs_out
   MXR_REQUIRE(hh != nullptr && pairs_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
               "mxr_proposal_pairs_read: bad argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   *images_out = 0;
   if (!h->pair_ptr || h->pair_images <= 0) return MXR_OK;
   MXR_CUDA(cudaDeviceSynchronize());

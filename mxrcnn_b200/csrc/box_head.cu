@@ -308,8 +308,9 @@ int mxr_box_head(mxr_handle_t hh, void* stream, const mxr_box_head_params* p, co
   MXR_TRY(check_params(p, "mxr_box_head"));
   MXR_REQUIRE(count_out != nullptr, MXR_ERR_INVALID, "mxr_box_head: NULL count_out");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   const int B = p->n_images, R = p->n_rois, C = p->n_classes;
   h->last_launches = 0;
   if (R == 0 || C < 2) {  // nothing to detect: every list is empty
@@ -350,7 +351,7 @@ int mxr_box_head_host(mxr_handle_t hh, const mxr_box_head_params* p, const float
   MXR_TRY(check_params(p, "mxr_box_head_host"));
   MXR_REQUIRE(count_out != nullptr, MXR_ERR_INVALID, "mxr_box_head_host: NULL count_out");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t B = p->n_images, R = p->n_rois, C = p->n_classes;
   if (R == 0 || C < 2) {
     memset(count_out, 0, B * C * 2 * sizeof(int32_t));
@@ -358,6 +359,7 @@ int mxr_box_head_host(mxr_handle_t hh, const mxr_box_head_params* p, const float
   }
   MXR_REQUIRE(rois && bbox_deltas && scores && im && dets_out && rows_out, MXR_ERR_INVALID, "mxr_box_head_host: NULL array");
   cudaStream_t s = h->stream;
+  MXR_TRY(ws_order(h, s));
   // workspace: [done counters | inputs | outputs]
   Carver probe(nullptr);
   probe.take<unsigned int>(B);

@@ -36,8 +36,9 @@ int mxr_bbox_pred(mxr_handle_t hh, void* stream, const void* boxes, int boxes_dt
   if (n == 0 || c4 == 0) return MXR_OK;  // bbox_transform.py:43-44: empty in, empty out
   MXR_REQUIRE(boxes && deltas && out, MXR_ERR_INVALID, "mxr_bbox_pred: NULL array");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   const long long total = (long long)n * (c4 / 4);
   const int grid = (int)((total + 255) / 256);
   h->last_launches = 0;
@@ -64,7 +65,7 @@ int mxr_bbox_pred_host(mxr_handle_t hh, const void* boxes, int boxes_dtype, cons
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_bbox_pred_host: NULL handle");
   if (n <= 0 || c4 <= 0) return n < 0 || c4 < 0 ? MXR_ERR_INVALID : MXR_OK;
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t bs = (size_t)n * 4 * (boxes_dtype == MXR_DTYPE_F64 ? 8 : 4);
   const size_t ds = (size_t)n * c4 * (deltas_dtype == MXR_DTYPE_F64 ? 8 : 4);
   const size_t os = (size_t)n * c4 * 8;
@@ -87,8 +88,9 @@ int mxr_clip_boxes(mxr_handle_t hh, void* stream, void* boxes, int dtype, int n,
   if (n == 0 || c4 == 0) return MXR_OK;
   MXR_REQUIRE(boxes != nullptr, MXR_ERR_INVALID, "mxr_clip_boxes: NULL array");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   const long long total = (long long)n * c4;
   const int grid = (int)((total + 255) / 256);
   h->last_launches = 0;
@@ -110,7 +112,7 @@ int mxr_clip_boxes_host(mxr_handle_t hh, void* boxes, int dtype, int n, int c4, 
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_clip_boxes_host: NULL handle");
   if (n <= 0 || c4 <= 0) return n < 0 || c4 < 0 ? MXR_ERR_INVALID : MXR_OK;
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t bs = (size_t)n * c4 * (dtype == MXR_DTYPE_F64 ? 8 : 4);
   MXR_TRY(ensure_device_ws(h, bs));
   MXR_CUDA(cudaMemcpyAsync(h->d_ws, boxes, bs, cudaMemcpyHostToDevice, h->stream));
@@ -128,8 +130,9 @@ int mxr_bbox_transform(mxr_handle_t hh, void* stream, const void* ex, int ex_dty
   if (n == 0) return MXR_OK;
   MXR_REQUIRE(ex && gt && out, MXR_ERR_INVALID, "mxr_bbox_transform: NULL array");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   h->last_launches = 0;
   const int g = (n + 255) / 256;
   prof_begin(h, s, ST_BOXES);
@@ -154,7 +157,7 @@ int mxr_bbox_transform_host(mxr_handle_t hh, const void* ex, int ex_dtype, const
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_bbox_transform_host: NULL handle");
   if (n <= 0) return n < 0 ? MXR_ERR_INVALID : MXR_OK;
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t es = (size_t)n * 4 * (ex_dtype == MXR_DTYPE_F64 ? 8 : 4);
   const size_t gs = (size_t)n * 4 * (gt_dtype == MXR_DTYPE_F64 ? 8 : 4);
   const size_t os = (size_t)n * 4 * ((ex_dtype == MXR_DTYPE_F32 && gt_dtype == MXR_DTYPE_F32) ? 4 : 8);
@@ -177,8 +180,9 @@ int mxr_bbox_overlaps(mxr_handle_t hh, void* stream, const double* boxes, int n,
   MXR_REQUIRE(n >= 0 && k >= 0 && box_stride >= 4 && query_stride >= 4, MXR_ERR_INVALID,
               "mxr_bbox_overlaps: bad shape n=%d k=%d strides %d/%d", n, k, box_stride, query_stride);
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   h->last_launches = 0;
   if (col_max && k > 0) MXR_CUDA(cudaMemsetAsync(col_max, 0, (size_t)k * sizeof(double), s));  // overlaps are >= 0
   if (n == 0 || k == 0) return MXR_OK;
@@ -206,7 +210,7 @@ int mxr_bbox_overlaps_host(mxr_handle_t hh, const double* boxes, int n, int box_
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_bbox_overlaps_host: NULL handle");
   MXR_REQUIRE(n >= 0 && k >= 0, MXR_ERR_INVALID, "mxr_bbox_overlaps_host: bad shape");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   Staged st(h);
   const size_t bb = (size_t)n * box_stride * 8, qb = (size_t)k * query_stride * 8;
   const size_t ob = st.reserve(bb ? bb : 8), oq = st.reserve(qb ? qb : 8);
@@ -235,8 +239,9 @@ int mxr_expand_bbox_targets(mxr_handle_t hh, void* stream, const float* data, in
   if (k == 0) return MXR_OK;
   MXR_REQUIRE(data && targets && weights, MXR_ERR_INVALID, "mxr_expand_bbox_targets: NULL array");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   float4 iw = make_float4(inside_weights4[0], inside_weights4[1], inside_weights4[2], inside_weights4[3]);
   const long long total = (long long)k * num_classes;
   h->last_launches = 0;
@@ -252,7 +257,7 @@ int mxr_expand_bbox_targets_host(mxr_handle_t hh, const float* data, int k, int 
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_expand_bbox_targets_host: NULL handle");
   if (k <= 0) return k < 0 ? MXR_ERR_INVALID : MXR_OK;
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   Staged st(h);
   const size_t db = (size_t)k * 5 * 4, tb = (size_t)k * 4 * num_classes * 4;
   const size_t od = st.reserve(db), ot = st.reserve(tb), ow = st.reserve(tb);

@@ -110,6 +110,10 @@ struct Handle {
   int pair_images;
   void* ctrl_ptr;       // device: control blocks of the last proposal call (mxr_proposal_counts)
   int ctrl_images;
+  // stream that last enqueued work on the handle's workspace / pinned block (ws_order)
+  cudaStream_t ws_last;
+  int ws_used, ws_last_private;
+  cudaEvent_t ev2;
   unsigned long long* dbg_ptr;  // device: phase time stamps of the last fused proposal call ([dbg_images][16])
   int dbg_images;
   cudaStream_t stream2;  // second private stream: slot 1 of the pipelined host path
@@ -129,6 +133,35 @@ static inline void prof_end(Handle* h, cudaStream_t s) {
   cudaEventRecord(h->prof[h->prof_used].b, s);
   h->prof_used++;
 }
+
+// Makes the calling thread's current device the handle's for the duration of an entry point and puts the caller's
+// back afterwards (a framework that drives several GPUs from one thread must not find its device changed).
+struct DeviceGuard {
+  int prev;
+  bool changed, good;
+  explicit DeviceGuard(int dev) : prev(-1), changed(false), good(true) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) {
+      good = cudaSetDevice(dev) == cudaSuccess;
+      changed = good && prev >= 0;
+    }
+  }
+  ~DeviceGuard() {
+    if (changed) cudaSetDevice(prev);
+  }
+};
+#define MXR_DEVICE(h_)                                                                          \
+  mxr::DeviceGuard dev_guard_((h_)->device);                                                    \
+  if (!dev_guard_.good) {                                                                       \
+    mxr::set_error("cudaSetDevice(%d) failed: %s", (h_)->device, cudaGetErrorString(cudaGetLastError())); \
+    return MXR_ERR_CUDA;                                                                        \
+  }
+
+// The handle's workspace and pinned block are shared by every entry point.  Work enqueued on the handle's own streams
+// orders itself; work on a caller's stream does not: before stream `s` touches the workspace, make it wait for what the
+// previous user stream still has queued (an event recorded there now -- conservative, no cost while the stream stays
+// the same).  Call it in every entry point once the stream is known, before anything is enqueued.
+int ws_order(Handle* h, cudaStream_t s);
 
 // Grow-only workspaces.  Growth synchronises the device (never in steady state).
 int ensure_device_ws(Handle* h, size_t bytes);

@@ -53,7 +53,7 @@ int run_stream(Handle* h, int iters, double* gops) {
 extern "C" int mxr_bench_alu_peak(mxr_handle_t hh, int dtype, double* gops_out) {
   MXR_REQUIRE(hh != nullptr && gops_out != nullptr, MXR_ERR_INVALID, "mxr_bench_alu_peak: NULL argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   MXR_TRY(ensure_device_ws(h, 4096));
   if (dtype == MXR_DTYPE_F64) return run_stream<double>(h, 4096, gops_out);
   if (dtype == MXR_DTYPE_F32) return run_stream<float>(h, 16384, gops_out);

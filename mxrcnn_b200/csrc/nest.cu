@@ -54,8 +54,9 @@ int mxr_nest(mxr_handle_t hh, void* stream, const void* dets, int n, int dtype, 
   if (n == 0) return MXR_OK;
   MXR_REQUIRE(dets && keep_flag, MXR_ERR_INVALID, "mxr_nest: NULL array");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   h->last_launches = 0;
   prof_begin(h, s, ST_BOXES);
   if (dtype == MXR_DTYPE_F64)
@@ -75,7 +76,7 @@ int mxr_nest_host(mxr_handle_t hh, const void* dets, int n, int dtype, double th
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nest_host: NULL handle");
   if (n <= 0) return n < 0 ? MXR_ERR_INVALID : MXR_OK;
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t db = (size_t)n * 5 * (dtype == MXR_DTYPE_F64 ? 8 : 4);
   const size_t off = align_up(db, 256);
   MXR_TRY(ensure_device_ws(h, off + (size_t)n * 4));

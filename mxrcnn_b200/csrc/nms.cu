@@ -251,6 +251,7 @@ int run(Handle* h, cudaStream_t s, const void* dets, bool dets_on_host, const in
   const size_t esize = dtype == MXR_DTYPE_F64 ? 8 : 4;
   NmsLayout L;
   make_layout(P, n_max, n_total, max_keep, esize, dets_on_host, nullptr, &L);
+  MXR_TRY(ws_order(h, s));
   MXR_TRY(ensure_device_ws(h, L.total));
   make_layout(P, n_max, n_total, max_keep, esize, dets_on_host, h->d_ws, &L);
   const size_t off_bytes = (size_t)(P + 1) * sizeof(int);
@@ -310,7 +311,7 @@ int mxr_nms(mxr_handle_t hh, void* stream, const void* dets, int n, int dtype, d
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms: NULL handle");
   MXR_REQUIRE(n >= 0, MXR_ERR_INVALID, "mxr_nms: n < 0");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const int32_t offs[2] = {0, n};
   return run(h, (cudaStream_t)stream, dets, false, offs, 1, dtype, thresh, max_keep, keep_out,
              nkeep_out);
@@ -321,7 +322,7 @@ int mxr_nms_host(mxr_handle_t hh, const void* dets, int n, int dtype, double thr
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms_host: NULL handle");
   MXR_REQUIRE(n >= 0, MXR_ERR_INVALID, "mxr_nms_host: n < 0");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const int32_t offs[2] = {0, n};
   return run(h, h->stream, dets, true, offs, 1, dtype, thresh, max_keep, keep_out, nkeep_out);
 }
@@ -330,7 +331,7 @@ int mxr_nms_batched(mxr_handle_t hh, void* stream, const void* dets, const int32
                     double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms_batched: NULL handle");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   return run(h, (cudaStream_t)stream, dets, false, offsets, n_problems, dtype, thresh, max_keep,
              keep_out, nkeep_out);
 }

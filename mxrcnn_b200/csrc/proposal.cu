@@ -529,13 +529,19 @@ int enqueue(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const Layou
   return MXR_OK;
 }
 
-__global__ void pad_rows_kernel(float* rois, float* scores, int row0, int nkeep, const int* __restrict__ src, int n_pad) {
+// proposal.py:135-141: rows nkeep ... nkeep + n - 1 of an image repeat kept rows drawn by the host.  The draws travel as a
+// kernel argument (up to kPadChunk per launch): no staging buffer, nothing to synchronise with.
+static const int kPadChunk = 768;
+struct PadRows {
+  int src[kPadChunk];
+};
+__global__ void pad_rows_kernel(float* rois, float* scores, int row0, int nkeep, int first, int n, const __grid_constant__ PadRows pr) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n_pad) return;
-  const int sidx = src[t];
+  if (t >= n) return;
+  const int sidx = pr.src[t];
   if (sidx < 0 || sidx >= nkeep) return;
-  for (int k = 0; k < 5; ++k) rois[(size_t)(row0 + nkeep + t) * 5 + k] = rois[(size_t)(row0 + sidx) * 5 + k];
-  if (scores) scores[row0 + nkeep + t] = scores[row0 + sidx];
+  for (int k = 0; k < 5; ++k) rois[(size_t)(row0 + nkeep + first + t) * 5 + k] = rois[(size_t)(row0 + sidx) * 5 + k];
+  if (scores) scores[row0 + nkeep + first + t] = scores[row0 + sidx];
 }
 
 }  // namespace
@@ -545,7 +551,7 @@ extern "C" {
 int mxr_reserve_proposal(mxr_handle_t hh, const mxr_proposal_params* p) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_reserve_proposal: NULL handle");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   Layout L;
   MXR_TRY(make_layout(p, p->post_nms_top_n > 0 ? p->post_nms_top_n : p->num_anchors * p->height * p->width, true,
                       nullptr, &L));
@@ -562,12 +568,13 @@ int mxr_proposal_forward(mxr_handle_t hh, void* stream, const mxr_proposal_param
   MXR_REQUIRE(cls_prob && bbox_pred && im_info && anchors && out_rois && out_nkeep, MXR_ERR_INVALID,
               "mxr_proposal_forward: NULL array argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   Layout L;
   MXR_TRY(make_layout(p, out_capacity, false, nullptr, &L));
   MXR_TRY(ensure_device_ws(h, L.total));
   MXR_TRY(make_layout(p, out_capacity, false, h->d_ws, &L));
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   const size_t hw = (size_t)L.H * L.W;
   return enqueue(h, s, p, L, cls_prob, 2 * L.A * hw, L.A * hw, bbox_pred, im_info, anchors, out_rois, out_scores,
                  out_keep, out_anchor_index, out_nkeep);
@@ -588,7 +595,7 @@ static int submit_host_impl(mxr_handle_t hh, int slot, const mxr_proposal_params
   MXR_REQUIRE(((cls_prob && bbox_pred && im_info) || packed) && anchors, MXR_ERR_INVALID,
               "mxr_proposal_submit_host: NULL array argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   if (!h->prop_state) {
     h->prop_state = calloc(1, sizeof(HostSlots));
     MXR_REQUIRE(h->prop_state != nullptr, MXR_ERR_NOMEM, "mxr_proposal_submit_host: out of host memory");
@@ -609,6 +616,7 @@ static int submit_host_impl(mxr_handle_t hh, int slot, const mxr_proposal_params
   }
   MXR_TRY(make_layout(p, out_capacity, true, h->d_ws + (size_t)slot * (h->d_bytes / 2 / 256 * 256), &L));
   cudaStream_t s = slot ? h->stream2 : h->stream;
+  MXR_TRY(ws_order(h, s));
   const size_t hw = (size_t)L.H * L.W;
   const size_t fg_bytes = (size_t)L.A * hw * sizeof(float);
   if (packed) {  // foreground scores | deltas | im_info, as the device block is laid out: one copy
@@ -654,7 +662,7 @@ int mxr_proposal_wait_host(mxr_handle_t hh, int slot, float* out_rois, float* ou
   Handle* h = reinterpret_cast<Handle*>(hh);
   HostSlots* hs = reinterpret_cast<HostSlots*>(h->prop_state);
   MXR_REQUIRE(hs && hs->busy[slot], MXR_ERR_INVALID, "mxr_proposal_wait_host: nothing was submitted to slot %d", slot);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const Layout& L = hs->L[slot];
   MXR_CUDA(cudaStreamSynchronize(slot ? h->stream2 : h->stream));
   hs->busy[slot] = 0;
@@ -688,7 +696,7 @@ int mxr_decode_clip(mxr_handle_t hh, void* stream, const mxr_proposal_params* p,
   MXR_REQUIRE(hh != nullptr && bbox_pred && im_info && anchors && out_boxes && out_valid, MXR_ERR_INVALID,
               "mxr_decode_clip: NULL argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   Layout L;
   MXR_TRY(make_layout(p, 1, false, nullptr, &L));
   AnchorTable at;
@@ -721,7 +729,7 @@ int mxr_proposal_counts(mxr_handle_t hh, int max_images, int32_t* counts_out, in
   MXR_REQUIRE(hh != nullptr && counts_out != nullptr && images_out != nullptr && max_images >= 1, MXR_ERR_INVALID,
               "mxr_proposal_counts: bad argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   *images_out = 0;
   if (!h->ctrl_ptr || h->ctrl_images <= 0) return MXR_OK;
   MXR_CUDA(cudaDeviceSynchronize());
@@ -752,16 +760,14 @@ int mxr_proposal_pad(mxr_handle_t hh, void* stream, int image, int rows_per_imag
   MXR_REQUIRE(pad_rows != nullptr && nkeep + n_pad <= rows_per_image && image >= 0, MXR_ERR_INVALID,
               "mxr_proposal_pad: bad pad request nkeep=%d n_pad=%d rows=%d", nkeep, n_pad, rows_per_image);
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
-  // the draws ride in the pinned staging block; the copy is ordered on the stream
-  MXR_TRY(ensure_pinned_ws(h, (size_t)n_pad * sizeof(int)));
-  MXR_TRY(ensure_device_ws(h, (size_t)n_pad * sizeof(int) + 256));
-  MXR_CUDA(cudaStreamSynchronize(s));  // staging block may still be in use by an earlier call
-  memcpy(h->h_pin, pad_rows, (size_t)n_pad * sizeof(int));
-  int* d_src = reinterpret_cast<int*>(h->d_ws);
-  MXR_CUDA(cudaMemcpyAsync(d_src, h->h_pin, (size_t)n_pad * sizeof(int), cudaMemcpyHostToDevice, s));
-  pad_rows_kernel<<<(n_pad + 127) / 128, 128, 0, s>>>(out_rois, out_scores, image * rows_per_image, nkeep, d_src, n_pad);
+  PadRows pr;
+  for (int first = 0; first < n_pad; first += kPadChunk) {
+    const int n = n_pad - first < kPadChunk ? n_pad - first : kPadChunk;
+    memcpy(pr.src, pad_rows + first, (size_t)n * sizeof(int));
+    pad_rows_kernel<<<(n + 127) / 128, 128, 0, s>>>(out_rois, out_scores, image * rows_per_image, nkeep, first, n, pr);
+  }
   MXR_CUDA(cudaGetLastError());
   return MXR_OK;
 }

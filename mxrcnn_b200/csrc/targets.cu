@@ -53,7 +53,7 @@ int mxr_anchor_target_phase1(mxr_handle_t hh, const mxr_anchor_target_params* p,
   const long long N = (long long)p->num_anchors * p->feat_height * p->feat_width;
   MXR_REQUIRE(N <= (1 << 24), MXR_ERR_LIMIT, "mxr_anchor_target_phase1: %lld anchors exceed the maximum of 16777216", N);
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   if (!h->at_state) {
     h->at_state = calloc(1, sizeof(AnchorTargetState));
     MXR_REQUIRE(h->at_state != nullptr, MXR_ERR_NOMEM, "mxr_anchor_target_phase1: out of host memory");
@@ -74,6 +74,7 @@ int mxr_anchor_target_phase1(mxr_handle_t hh, const mxr_anchor_target_params* p,
   at_layout(g, h->d_ws, st);
   MXR_TRY(ensure_pinned_ws(h, 4 * sizeof(int)));
   cudaStream_t s = h->stream;
+  MXR_TRY(ws_order(h, s));
   AnchorTable at;
   memset(&at, 0, sizeof(at));
   memcpy(at.a, anchors, sizeof(double) * 4 * g.A);
@@ -136,7 +137,7 @@ int mxr_anchor_target_phase2(mxr_handle_t hh, void* stream, const int32_t* fg_di
   Handle* h = reinterpret_cast<Handle*>(hh);
   AnchorTargetState* st = reinterpret_cast<AnchorTargetState*>(h->at_state);
   MXR_REQUIRE(st && st->valid, MXR_ERR_INVALID, "mxr_anchor_target_phase2: call mxr_anchor_target_phase1 first");
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   // phase 1 ran on the handle's stream and was synchronised, so its results are visible to any stream
   MXR_TRY(at_phase2(h, (cudaStream_t)stream, st, fg_disable_ranks, n_fg_disable, bg_disable_ranks, n_bg_disable, positive_weight,
                     negative_weight, inside_weights4, label, bbox_target, bbox_inside_weight, bbox_outside_weight));
@@ -153,10 +154,11 @@ int mxr_anchor_target_phase2_host(mxr_handle_t hh, const int32_t* fg_disable_ran
   Handle* h = reinterpret_cast<Handle*>(hh);
   AnchorTargetState* st = reinterpret_cast<AnchorTargetState*>(h->at_state);
   MXR_REQUIRE(st && st->valid, MXR_ERR_INVALID, "mxr_anchor_target_phase2_host: call mxr_anchor_target_phase1 first");
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t N = st->g.N;
   float* d = reinterpret_cast<float*>(st->d_out);
   cudaStream_t s = h->stream;
+  MXR_TRY(ws_order(h, s));
   MXR_TRY(at_phase2(h, s, st, fg_disable_ranks, n_fg_disable, bg_disable_ranks, n_bg_disable, positive_weight, negative_weight,
                     inside_weights4, d, d + N, d + 5 * N, d + 9 * N));
   MXR_CUDA(cudaMemcpyAsync(label, d, N * 4, cudaMemcpyDeviceToHost, s));
@@ -174,8 +176,9 @@ int mxr_fg_bg_lists(mxr_handle_t hh, void* stream, const void* overlaps, int dty
   MXR_REQUIRE(hh != nullptr && counts != nullptr, MXR_ERR_INVALID, "mxr_fg_bg_lists: NULL argument");
   MXR_REQUIRE(n >= 0 && (n == 0 || (overlaps && fg_list && bg_list)), MXR_ERR_INVALID, "mxr_fg_bg_lists: bad arrays");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   h->last_launches = 0;
   prof_begin(h, s, ST_PROPOSAL_TARGET);
   if (dtype == MXR_DTYPE_F64)
@@ -196,7 +199,7 @@ int mxr_fg_bg_lists_host(mxr_handle_t hh, const void* overlaps, int dtype, int n
                          int32_t* fg_list, int32_t* bg_list, int32_t* counts) {
   MXR_REQUIRE(hh != nullptr && counts != nullptr && n >= 0, MXR_ERR_INVALID, "mxr_fg_bg_lists_host: bad argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t es = dtype == MXR_DTYPE_F64 ? 8 : 4;
   Carver c(nullptr);
   c.take<char>((size_t)n * es + 8);
@@ -210,6 +213,7 @@ int mxr_fg_bg_lists_host(mxr_handle_t hh, const void* overlaps, int dtype, int n
   int* d_bg = d.take<int>(n + 1);
   int* d_cnt = d.take<int>(2);
   cudaStream_t s = h->stream;
+  MXR_TRY(ws_order(h, s));
   if (n) MXR_CUDA(cudaMemcpyAsync(d_ov, overlaps, (size_t)n * es, cudaMemcpyHostToDevice, s));
   MXR_TRY(mxr_fg_bg_lists(hh, s, d_ov, dtype, n, fg_thresh, bg_hi, bg_lo, d_fg, d_bg, d_cnt));
   if (n) {
@@ -249,8 +253,9 @@ int mxr_proposal_target_gather(mxr_handle_t hh, void* stream, const mxr_proposal
   MXR_REQUIRE(rois && gt_boxes && gt_assignment && keep_inds && out_rois && labels && bbox_targets && inside && outside,
               MXR_ERR_INVALID, "mxr_proposal_target_gather: NULL array");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
   a.rois = rois;
   a.gt = gt_boxes;
   a.assignment = gt_assignment;
@@ -274,7 +279,7 @@ int mxr_proposal_target_gather_host(mxr_handle_t hh, const mxr_proposal_target_p
                                     float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside) {
   MXR_REQUIRE(hh != nullptr && p != nullptr, MXR_ERR_INVALID, "mxr_proposal_target_gather_host: NULL argument");
   Handle* h = reinterpret_cast<Handle*>(hh);
-  MXR_CUDA(cudaSetDevice(h->device));
+  MXR_DEVICE(h);
   const size_t R = p->num_rois, G = p->num_gt, K = p->num_keep, C4 = 4 * (size_t)p->num_classes;
   if (K == 0) return MXR_OK;
   for (int pass = 0; pass < 2; ++pass) {
@@ -293,6 +298,7 @@ int mxr_proposal_target_gather_host(mxr_handle_t hh, const mxr_proposal_target_p
       continue;
     }
     cudaStream_t s = h->stream;
+    MXR_TRY(ws_order(h, s));
     MXR_CUDA(cudaMemcpyAsync(d_rois, rois, R * 5 * 4, cudaMemcpyHostToDevice, s));
     MXR_CUDA(cudaMemcpyAsync(d_gt, gt_boxes, G * 5 * 4, cudaMemcpyHostToDevice, s));
     MXR_CUDA(cudaMemcpyAsync(d_as, gt_assignment, R * 4, cudaMemcpyHostToDevice, s));

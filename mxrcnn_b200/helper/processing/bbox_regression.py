@@ -7,7 +7,7 @@ from .bbox_transform import bbox_transform  # noqa: F401  (the reference re-expo
 
 
 def _overlaps_call(boxes, query_boxes, want_matrix, want_reductions):
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, boxes)
     if _lib.is_device_array(boxes):
         import torch
         b = boxes.double().contiguous()
@@ -51,7 +51,7 @@ def bbox_overlaps_reduced(boxes, query_boxes):
 def expand_bbox_regression_targets(bbox_targets_data, num_classes):
     """(k,5) [cls,dx,dy,dw,dh] -> ((k,4C) targets, (k,4C) inside weights), float32
     (reference: bbox_regression.py:67-85)."""
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, bbox_targets_data)
     iw = np.ascontiguousarray(config.TRAIN.BBOX_INSIDE_WEIGHTS, dtype=np.float32)
     if _lib.is_device_array(bbox_targets_data):
         import torch

@@ -22,7 +22,7 @@ def bbox_transform(ex_rois, gt_rois):
     """Regression targets from ex_rois to gt_rois, (N,4) each (reference: bbox_transform.py:8-32).
     Like numpy, each side is evaluated in its own dtype and the result in the promoted one
     (float32 only when both inputs are float32)."""
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, ex_rois)
     if _lib.is_device_array(ex_rois):
         import torch
         ex = (ex_rois if ex_rois.dtype in (torch.float32, torch.float64) else ex_rois.double())[:, :4].contiguous()
@@ -51,7 +51,7 @@ def bbox_pred(boxes, box_deltas, is_train=False):
     ``is_train`` (never enabled by any caller of the reference, and under py3 its ``map`` form does
     not even run) clamps |dx|,|dy| to 10 and |dw|,|dh| to 8 elementwise before the transform (:56-64).
     """
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, boxes)
     if _lib.is_device_array(boxes):
         import torch
         n, c4 = box_deltas.shape
@@ -92,7 +92,7 @@ def _clamp_train(d, xp):
 def clip_boxes(boxes, im_shape):
     """Clip (N, 4*num_classes) boxes to the image, IN PLACE, and return the same array
     (reference: bbox_transform.py:81-96).  x limits come from im_shape[1], y from im_shape[0]."""
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, boxes)
     lim_x, lim_y = float(im_shape[1] - 1), float(im_shape[0] - 1)  # numpy scalar rules apply to the subtraction
     if _lib.is_device_array(boxes):
         import torch

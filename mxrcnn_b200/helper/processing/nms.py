@@ -16,7 +16,7 @@ def nms(dets, thresh, max_keep=0, handle=None):
     ``max_keep`` > 0 (extension) stops after that many boxes.
     """
     lib = _lib.load()
-    h = handle or _lib.default_handle()
+    h = _lib.handle_for(handle, dets)
     if _lib.is_device_array(dets):
         v = _lib.device_view(dets)
         if v.dtype not in (np.float32, np.float64) or len(v.shape) != 2 or v.shape[1] != 5:
@@ -55,7 +55,7 @@ def nms_batched(dets_list, thresh, max_keep=0, handle=None):
     as ONE launch.  ``dets_list``: list of (n_c,5) numpy arrays of one dtype (float32 or float64).
     Returns a list of python lists, element c equal to ``nms(dets_list[c], thresh)``."""
     lib = _lib.load()
-    h = handle or _lib.default_handle()
+    h = _lib.handle_for(handle, dets_list)
     if len(dets_list) == 0:
         return []
     dt = np.float32 if all(np.asarray(d).dtype == np.float32 for d in dets_list) else np.float64
@@ -83,7 +83,7 @@ def nest(dets, thresh=0.90):
     """Drop every box that lies (almost) inside another one: box i goes when inter(i,j)/area(i) > thresh
     for some j != i (reference: helper/processing/nms.py:40-70, called from predict.py:75).
     Returns the python list of kept row indices, ascending."""
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, dets)
     d = np.asarray(dets)
     if d.ndim != 2 or d.shape[1] < 4:
         raise ValueError("dets must be (n, >=4)")

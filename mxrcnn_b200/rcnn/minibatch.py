@@ -25,7 +25,7 @@ def _fg_bg_lists(overlaps, fg_thresh, bg_hi, bg_lo):
     fg = np.empty((n,), dtype=np.int32)
     bg = np.empty((n,), dtype=np.int32)
     cnt = np.zeros((2,), dtype=np.int32)
-    _lib.check(_lib.load().mxr_fg_bg_lists_host(_lib.default_handle().ptr, _lib.hptr(ov),
+    _lib.check(_lib.load().mxr_fg_bg_lists_host(_lib.handle_for(None, overlaps).ptr, _lib.hptr(ov),
                                                 1 if ov.dtype == np.float64 else 0, n, float(fg_thresh), float(bg_hi),
                                                 float(bg_lo), _lib.hptr(fg), _lib.hptr(bg), _lib.hptr(cnt)))
     return fg[:cnt[0]].astype(np.int64), bg[:cnt[1]].astype(np.int64)
@@ -73,7 +73,7 @@ def assign_anchor(feat_shape, gt_boxes, im_info, feat_stride=16,
     DEVICE arrays of those shapes (e.g. one image's slices of the batch tensors); the results are written there on
     the arrays' current stream and never visit the host.
     """
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, *(tuple(out.values()) if out else ()))
     T = config.TRAIN
     info = np.asarray(im_info, dtype=np.float32)[0]
     scales_f32 = np.array(scales, dtype=np.float32)                 # minibatch.py:243

@@ -34,7 +34,7 @@ def proposal_forward(cls_prob, bbox_pred, im_info, anchors, feat_stride, pre_nms
     proposal.py:135-139 (one draw per short image, image order).
     """
     lib = _lib.load()
-    h = handle or _lib.default_handle()
+    h = _lib.handle_for(handle, cls_prob)
     on_device = _lib.is_device_array(cls_prob)
     if on_device:
         vc, vb, vi = _lib.device_view(cls_prob, np.float32), _lib.device_view(bbox_pred, np.float32), \

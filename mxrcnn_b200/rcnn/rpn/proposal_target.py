@@ -95,7 +95,7 @@ def _sample_rois(all_rois, gt_boxes, fg_rois_per_image, rois_per_image, num_clas
     """Random sample of RoIs with labels and class-expanded regression targets
     (reference: proposal_target.py:135-196).  Returns (labels, rois, bbox_targets, bbox_inside_weights).
     RNG order: fg (no replacement), fg padding (with replacement, if short), bg, bg padding."""
-    lib, h = _lib.load(), _lib.default_handle()
+    lib, h = _lib.load(), _lib.handle_for(None, all_rois)
     T = config.TRAIN
     rois_f32 = np.ascontiguousarray(all_rois, dtype=np.float32)
     gt_f32 = np.ascontiguousarray(gt_boxes, dtype=np.float32)

@@ -41,7 +41,7 @@ def detections_batch(scores, rois, bbox_deltas, im_shapes, scales, thresh=0.05, 
     """Extension: B images per launch.  scores (B,R,C), rois (B,R,4|5), bbox_deltas (B,R,4C); im_shapes and
     scales have one entry per image.  Returns a list of B ``boxes_this_image`` lists (and the rows)."""
     lib = _lib.load()
-    h = handle or _lib.default_handle()
+    h = _lib.handle_for(handle, scores)
     scores = _lib.host(scores, np.float32)
     rois = np.asarray(rois)
     if rois.ndim != 3 or rois.shape[2] not in (4, 5):
@@ -76,7 +76,7 @@ def detections_device(scores, rois, bbox_deltas, im, thresh=0.05, nms_thresh=Non
     ``dets`` (B,C,R,5) f64, ``rows`` (B,C,R) i32, ``count`` (B,C,2) i32 ([after the cap, after NMS])."""
     import torch
     lib = _lib.load()
-    h = handle or _lib.default_handle()
+    h = _lib.handle_for(handle, scores)
     vs, vr, vd = _lib.device_view(scores, np.float32), _lib.device_view(rois, np.float32), _lib.device_view(bbox_deltas, np.float32)
     vi = _lib.device_view(im, np.float64)
     B, R, C = vs.shape
