@@ -317,6 +317,20 @@ int mxr_proposal_target_gather_host(mxr_handle_t h, const mxr_proposal_target_pa
                                     const float* gt_boxes, const int32_t* gt_assignment, const int32_t* keep_inds,
                                     float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside);
 
+/* _sample_rois (proposal_target.py:135-196) in two calls with host arrays.  phase1: ONE launch computes the float64
+ * IoU of every roi with every gt box, argmax / max per roi (:140-144) and the ordered index lists the sampler draws
+ * from -- fg (max >= fg_thresh, :148), bg (bg_lo <= max < bg_hi, :160-161) and the TRAIN-mode fallback bg
+ * (fallback_lo <= max < fallback_hi, :162-166) -- and returns them in one copy (counts3 = their lengths;
+ * gt_assignment / max_overlaps optional).  The rois, gt boxes and assignments stay on the device.  The caller draws
+ * with numpy's RNG in the reference's order, then phase2 gathers the num_keep <= max_keep sampled rows exactly like
+ * mxr_proposal_target_gather and returns all five outputs in one copy.  phase2 consumes the state of phase1. */
+int mxr_proposal_target_phase1_host(mxr_handle_t h, const float* rois, int num_rois, const float* gt_boxes, int num_gt,
+                                    int max_keep, int num_classes, double fg_thresh, double bg_hi, double bg_lo,
+                                    double fallback_hi, double fallback_lo, int32_t* fg_list, int32_t* bg_list,
+                                    int32_t* fallback_list, int32_t* counts3, int32_t* gt_assignment, double* max_overlaps);
+int mxr_proposal_target_phase2_host(mxr_handle_t h, const mxr_proposal_target_params* p, const int32_t* keep_inds,
+                                    float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside);
+
 /* ---- nms without any allocation (no counterpart in the reference) --------------------- */
 /* Same result as mxr_nms on device arrays, for callers that cannot allocate GPU memory: a plug-in
  * inside a framework whose pool already owns the whole device (a cudaMalloc of ours would fail or

@@ -119,6 +119,10 @@ SIGNATURES = {
                                             ctypes.c_double, _VP, _VP, _VP]),
     "mxr_proposal_target_gather": (ctypes.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "mxr_proposal_target_gather_host": (ctypes.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "mxr_proposal_target_phase1_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                       ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,
+                                                       ctypes.c_double, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "mxr_proposal_target_phase2_host": (ctypes.c_int, [_VP, ctypes.POINTER(ProposalTargetParams), _VP, _VP, _VP, _VP, _VP, _VP]),
     "mxr_nms_noalloc": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
 }
 

@@ -145,6 +145,7 @@ int mxr_destroy(mxr_handle_t hh) {
   if (h->d_ws) cudaFree(h->d_ws);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->at_state) free(h->at_state);
+  if (h->pt_state) free(h->pt_state);
   if (h->prop_state) free(h->prop_state);
   if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->ev) cudaEventDestroy(h->ev);

@@ -100,6 +100,7 @@ struct Handle {
   int* cluster_cap;   // [4][8] fused proposal kernels (first generation 4 / 12 keys per thread, second generation 4 / 12)
                       // x cluster size (16, 14, ... 2): clusters resident at once; 0 not queried, -1 none
   void* at_state;     // anchor-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
+  void* pt_state;     // proposal-target state carried from phase 1 to phase 2 (malloc'd, targets.cu)
   int no_cluster;     // MXRCNN_B200_NO_CLUSTER=1: use the multi-kernel proposal path instead of the fused one
   int cluster_override; // MXRCNN_B200_CLUSTER=2|4|8|16 pins the cluster size of the fused proposal kernel (tests cover
                         // them all); MXRCNN_B200_CLUSTER8=1 is the older spelling of 8.  0: chosen per call

@@ -170,7 +170,10 @@ __device__ __noinline__ bool exact_min_size(const FusedArgs& g, float dx, float 
 __device__ __forceinline__ float pair_d(const Box32& r, const float4 cb, const float2 ca, float* tol) {
   const float xx1 = fmaxf(r.x1, cb.x), yy1 = fmaxf(r.y1, cb.y);
   const float xx2 = fminf(r.x2p, cb.z), yy2 = fminf(r.y2p, cb.w);
-  const float w = fmaxf(xx2 - xx1, 0.0f), h = fmaxf(yy2 - yy1, 0.0f);
+  // Only ONE extent is clamped at zero: with w >= 0 a negative h makes the product <= 0, i.e. "no overlap" decided as it
+  // should be, and an h within the error bound of zero changes the product by at most w * delta, which the tolerance
+  // covers (FMNMX runs at half rate: five of them per pair instead of six).
+  const float w = fmaxf(xx2 - xx1, 0.0f), h = yy2 - yy1;
   *tol = r.t + ca.y;
   return __fmaf_rn(w, h, -(r.a + ca.x));  // a screen, not the reference's arithmetic: contraction is welcome
 }

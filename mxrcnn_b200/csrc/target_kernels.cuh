@@ -286,6 +286,79 @@ static __global__ void __launch_bounds__(1024) fg_bg_lists_kernel(const T* __res
   }
 }
 
+// proposal_target.py:140-166 in ONE launch (one CTA): IoU of every roi with every gt box in float64, first-maximum
+// argmax and max per roi (:143-144), and the three ordered index lists the sampler draws from: fg (max >= FG_THRESH,
+// :148), bg (BG_THRESH_LO <= max < BG_THRESH_HI, :160-161) and the TRAIN-mode fallback bg (0 <= max < HI + 0.2, :162-166).
+// rois (R,5) f32 [batch index, x1, y1, x2, y2], gt (G,5) f32.  lists: [3][R] i32; counts: [3].
+static const int kPtChunk = 256;
+static __global__ void __launch_bounds__(1024) proposal_target_phase1_kernel(const float* __restrict__ rois, int R,
+                                                                      const float* __restrict__ gt, int G, double fg_thresh,
+                                                                      double bg_hi, double bg_lo, double fb_hi, double fb_lo,
+                                                                      int* __restrict__ assignment, double* __restrict__ maxov,
+                                                                      int* __restrict__ lists, int* __restrict__ counts) {
+  __shared__ double sq[kPtChunk][5];
+  __shared__ int s_warp[33];
+  int nf = 0, nb = 0, nfb = 0;
+  for (int i0 = 0; i0 < R; i0 += blockDim.x) {
+    const int i = i0 + threadIdx.x;
+    const bool live = i < R;
+    double bx1 = 0, by1 = 0, bx2 = 0, by2 = 0;
+    if (live) {  // all_rois[:, 1:5].astype(np.float), :141
+      bx1 = (double)rois[(size_t)i * 5 + 1];
+      by1 = (double)rois[(size_t)i * 5 + 2];
+      bx2 = (double)rois[(size_t)i * 5 + 3];
+      by2 = (double)rois[(size_t)i * 5 + 4];
+    }
+    double best = 0.0;
+    int arg = 0;
+    for (int q0 = 0; q0 < G; q0 += kPtChunk) {
+      const int qn = min(kPtChunk, G - q0);
+      __syncthreads();
+      for (int t = threadIdx.x; t < qn; t += blockDim.x) {
+        const float* q = gt + (size_t)(q0 + t) * 5;
+        const double x1 = (double)q[0], y1 = (double)q[1], x2 = (double)q[2], y2 = (double)q[3];
+        sq[t][0] = x1;
+        sq[t][1] = y1;
+        sq[t][2] = x2;
+        sq[t][3] = y2;
+        sq[t][4] = Ar<double>::mul(Ar<double>::add(Ar<double>::sub(x2, x1), 1.0), Ar<double>::add(Ar<double>::sub(y2, y1), 1.0));
+      }
+      __syncthreads();
+      if (live) {
+        for (int j = 0; j < qn; ++j) {
+          const double ov = overlap_one(bx1, by1, bx2, by2, sq[j][0], sq[j][1], sq[j][2], sq[j][3], sq[j][4]);
+          if ((q0 + j == 0) || ov > best) {
+            best = ov;
+            arg = q0 + j;
+          }
+        }
+      }
+    }
+    if (live) {
+      assignment[i] = arg;
+      maxov[i] = best;
+    }
+    const bool fg = live && (best >= fg_thresh);
+    const bool bg = live && (best < bg_hi) && (best >= bg_lo);
+    const bool fb = live && (best < fb_hi) && (best >= fb_lo);
+    int total;
+    int r = block_exclusive_rank(fg, s_warp, &total);
+    if (fg) lists[nf + r] = i;
+    nf += total;
+    r = block_exclusive_rank(bg, s_warp, &total);
+    if (bg) lists[R + nb + r] = i;
+    nb += total;
+    r = block_exclusive_rank(fb, s_warp, &total);
+    if (fb) lists[2 * R + nfb + r] = i;
+    nfb += total;
+  }
+  if (threadIdx.x == 0) {
+    counts[0] = nf;
+    counts[1] = nb;
+    counts[2] = nfb;
+  }
+}
+
 struct PtGather {
   const float* rois;       // (R,5)
   const float* gt;         // (G,5)

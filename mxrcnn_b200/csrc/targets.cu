@@ -19,6 +19,34 @@ struct AnchorTargetState {
   bool valid;
 };
 
+// State carried from mxr_proposal_target_phase1_host to _phase2_host: the rois, gt boxes and assignments stay on the
+// device, only the index lists and the sampled indices cross the bus.
+struct ProposalTargetState {
+  int R, G;
+  float* d_rois;
+  float* d_gt;
+  int* d_assign;
+  double* d_maxov;
+  int* d_lists;    // [3][R] + counts[3]
+  char* d_out;     // phase 2 outputs, contiguous
+  int* d_keep;
+  size_t out_cap;  // bytes of d_out
+  bool valid;
+};
+
+size_t pt_layout(int R, int G, int K, int C, char* base, ProposalTargetState* st) {
+  Carver c(base);
+  st->d_rois = c.take<float>((size_t)R * 5);
+  st->d_gt = c.take<float>((size_t)(G > 0 ? G : 1) * 5);
+  st->d_assign = c.take<int>(R);
+  st->d_maxov = c.take<double>(R);
+  st->d_lists = c.take<int>((size_t)3 * R + 4);
+  st->d_keep = c.take<int>(K > 0 ? K : 1);
+  st->out_cap = (size_t)K * (5 + 1 + 3 * 4 * (size_t)C) * sizeof(float);
+  st->d_out = c.take<char>(st->out_cap + 16);
+  return align_up(c.off, 256);
+}
+
 size_t at_layout(const AnchorTargetGeom& g, char* base, AnchorTargetState* st) {
   Carver c(base);
   const int N = g.N, G = g.G > 0 ? g.G : 1;
@@ -311,6 +339,95 @@ int mxr_proposal_target_gather_host(mxr_handle_t hh, const mxr_proposal_target_p
     MXR_CUDA(cudaMemcpyAsync(outside, d_o, K * C4 * 4, cudaMemcpyDeviceToHost, s));
     MXR_CUDA(cudaStreamSynchronize(s));
   }
+  return MXR_OK;
+}
+
+// ---- _sample_rois in two calls (proposal_target.py:135-196) ------------------------------------
+int mxr_proposal_target_phase1_host(mxr_handle_t hh, const float* rois, int num_rois, const float* gt_boxes, int num_gt,
+                                    int max_keep, int num_classes, double fg_thresh, double bg_hi, double bg_lo,
+                                    double fallback_hi, double fallback_lo, int32_t* fg_list, int32_t* bg_list,
+                                    int32_t* fallback_list, int32_t* counts3, int32_t* gt_assignment, double* max_overlaps) {
+  MXR_REQUIRE(hh != nullptr && rois && gt_boxes && fg_list && bg_list && fallback_list && counts3, MXR_ERR_INVALID,
+              "mxr_proposal_target_phase1_host: NULL argument");
+  MXR_REQUIRE(num_rois >= 1 && num_gt >= 1 && max_keep >= 1 && num_classes >= 1, MXR_ERR_INVALID,
+              "mxr_proposal_target_phase1_host: bad sizes R=%d G=%d K=%d C=%d", num_rois, num_gt, max_keep, num_classes);
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_DEVICE(h);
+  if (!h->pt_state) {
+    h->pt_state = calloc(1, sizeof(ProposalTargetState));
+    MXR_REQUIRE(h->pt_state != nullptr, MXR_ERR_NOMEM, "mxr_proposal_target_phase1_host: out of host memory");
+  }
+  ProposalTargetState* st = reinterpret_cast<ProposalTargetState*>(h->pt_state);
+  st->valid = false;
+  const int R = num_rois, G = num_gt;
+  cudaStream_t s = h->stream;
+  MXR_TRY(ws_order(h, s));
+  MXR_TRY(ensure_device_ws(h, pt_layout(R, G, max_keep, num_classes, nullptr, st)));
+  pt_layout(R, G, max_keep, num_classes, h->d_ws, st);
+  const size_t list_bytes = ((size_t)3 * R + 4) * sizeof(int);
+  MXR_TRY(ensure_pinned_ws(h, list_bytes + (size_t)R * 12 + st->out_cap + 64));
+  st->R = R;
+  st->G = G;
+  MXR_CUDA(cudaMemcpyAsync(st->d_rois, rois, (size_t)R * 5 * sizeof(float), cudaMemcpyHostToDevice, s));
+  MXR_CUDA(cudaMemcpyAsync(st->d_gt, gt_boxes, (size_t)G * 5 * sizeof(float), cudaMemcpyHostToDevice, s));
+  h->last_launches = 0;
+  prof_begin(h, s, ST_PROPOSAL_TARGET);
+  proposal_target_phase1_kernel<<<1, 1024, 0, s>>>(st->d_rois, R, st->d_gt, G, fg_thresh, bg_hi, bg_lo, fallback_hi, fallback_lo,
+                                                  st->d_assign, st->d_maxov, st->d_lists, st->d_lists + 3 * R);
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  // one copy back: the three lists and their counts (+ the assignments / overlaps when the caller wants them)
+  char* pin = h->h_pin;
+  MXR_CUDA(cudaMemcpyAsync(pin, st->d_lists, list_bytes, cudaMemcpyDeviceToHost, s));
+  if (gt_assignment) MXR_CUDA(cudaMemcpyAsync(pin + list_bytes, st->d_assign, (size_t)R * 4, cudaMemcpyDeviceToHost, s));
+  if (max_overlaps) MXR_CUDA(cudaMemcpyAsync(pin + list_bytes + (size_t)R * 4, st->d_maxov, (size_t)R * 8, cudaMemcpyDeviceToHost, s));
+  MXR_CUDA(cudaStreamSynchronize(s));
+  const int* hl = reinterpret_cast<const int*>(pin);
+  memcpy(counts3, hl + 3 * R, 3 * sizeof(int));
+  memcpy(fg_list, hl, (size_t)counts3[0] * sizeof(int));
+  memcpy(bg_list, hl + R, (size_t)counts3[1] * sizeof(int));
+  memcpy(fallback_list, hl + 2 * R, (size_t)counts3[2] * sizeof(int));
+  if (gt_assignment) memcpy(gt_assignment, pin + list_bytes, (size_t)R * 4);
+  if (max_overlaps) memcpy(max_overlaps, pin + list_bytes + (size_t)R * 4, (size_t)R * 8);
+  st->valid = true;
+  return MXR_OK;
+}
+
+int mxr_proposal_target_phase2_host(mxr_handle_t hh, const mxr_proposal_target_params* p, const int32_t* keep_inds,
+                                    float* out_rois, float* labels, float* bbox_targets, float* inside, float* outside) {
+  MXR_REQUIRE(hh != nullptr && p != nullptr, MXR_ERR_INVALID, "mxr_proposal_target_phase2_host: NULL argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  ProposalTargetState* st = reinterpret_cast<ProposalTargetState*>(h->pt_state);
+  MXR_REQUIRE(st && st->valid, MXR_ERR_INVALID, "mxr_proposal_target_phase2_host: call mxr_proposal_target_phase1_host first");
+  MXR_REQUIRE(p->num_rois == st->R && p->num_gt == st->G, MXR_ERR_INVALID,
+              "mxr_proposal_target_phase2_host: sizes differ from phase 1 (R %d vs %d, G %d vs %d)", p->num_rois, st->R,
+              p->num_gt, st->G);
+  MXR_DEVICE(h);
+  const size_t K = p->num_keep, C4 = 4 * (size_t)p->num_classes;
+  st->valid = false;
+  if (K == 0) return MXR_OK;
+  MXR_REQUIRE(keep_inds && out_rois && labels && bbox_targets && inside && outside, MXR_ERR_INVALID,
+              "mxr_proposal_target_phase2_host: NULL array");
+  const size_t need = K * (5 + 1 + 3 * C4) * sizeof(float);
+  MXR_REQUIRE(need <= st->out_cap, MXR_ERR_INVALID, "mxr_proposal_target_phase2_host: num_keep %zu exceeds phase 1's max_keep", K);
+  cudaStream_t s = h->stream;
+  MXR_TRY(ws_order(h, s));
+  MXR_CUDA(cudaMemcpyAsync(st->d_keep, keep_inds, K * sizeof(int), cudaMemcpyHostToDevice, s));
+  float* d = reinterpret_cast<float*>(st->d_out);
+  float* d_or = d;
+  float* d_lab = d_or + K * 5;
+  float* d_t = d_lab + K;
+  float* d_i = d_t + K * C4;
+  float* d_o = d_i + K * C4;
+  MXR_TRY(mxr_proposal_target_gather(hh, s, p, st->d_rois, st->d_gt, st->d_assign, st->d_keep, d_or, d_lab, d_t, d_i, d_o));
+  MXR_CUDA(cudaMemcpyAsync(h->h_pin, d, need, cudaMemcpyDeviceToHost, s));  // ONE copy, then split on the host
+  MXR_CUDA(cudaStreamSynchronize(s));
+  const float* hp = reinterpret_cast<const float*>(h->h_pin);
+  memcpy(out_rois, hp, K * 5 * sizeof(float));
+  memcpy(labels, hp + K * 5, K * sizeof(float));
+  memcpy(bbox_targets, hp + K * 6, K * C4 * sizeof(float));
+  memcpy(inside, hp + K * 6 + K * C4, K * C4 * sizeof(float));
+  memcpy(outside, hp + K * 6 + 2 * K * C4, K * C4 * sizeof(float));
   return MXR_OK;
 }
 

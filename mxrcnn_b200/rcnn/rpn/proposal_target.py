@@ -101,10 +101,18 @@ def _sample_rois(all_rois, gt_boxes, fg_rois_per_image, rois_per_image, num_clas
     gt_f32 = np.ascontiguousarray(gt_boxes, dtype=np.float32)
     if gt_f32.shape[0] == 0:
         raise ValueError("attempt to get argmax of an empty sequence")  # overlaps.argmax(axis=1) on (n,0), :143
-    # IoU + argmax + max on the GPU, float64 like the reference (:140-144)
-    gt_assignment, max_overlaps, _ = bbox_overlaps_reduced(
-        np.ascontiguousarray(rois_f32[:, 1:5], dtype=np.float64), np.ascontiguousarray(gt_f32[:, :4], dtype=np.float64))
-    fg_inds, bg_inds_ = _fg_bg_lists(max_overlaps, T.FG_THRESH, T.BG_THRESH_HI, T.BG_THRESH_LO)
+    # ONE launch: IoU + argmax + max in float64 like the reference (:140-144) and the three index lists the sampler may
+    # draw from (:148, :160-166); rois, gt boxes and assignments stay on the device for the gather below
+    R, G = rois_f32.shape[0], gt_f32.shape[0]
+    fg_buf, bg_buf, fb_buf = (np.empty((R,), dtype=np.int32) for _ in range(3))
+    cnt = np.zeros((3,), dtype=np.int32)
+    c4 = 4 * int(num_classes)
+    _lib.check(lib.mxr_proposal_target_phase1_host(
+        h.ptr, _lib.hptr(rois_f32), R, _lib.hptr(gt_f32), G, int(rois_per_image), int(num_classes), float(T.FG_THRESH),
+        float(T.BG_THRESH_HI), float(T.BG_THRESH_LO), float(T.BG_THRESH_HI + 0.2), 0.0, _lib.hptr(fg_buf), _lib.hptr(bg_buf),
+        _lib.hptr(fb_buf), _lib.hptr(cnt), None, None))
+    fg_inds = fg_buf[:cnt[0]].astype(np.int64)
+    bg_inds_ = bg_buf[:cnt[1]].astype(np.int64)
     fg_rois_per_this_image = min(fg_rois_per_image, fg_inds.size)
     if fg_inds.size > 0:
         fg_inds = npr.choice(fg_inds, size=fg_rois_per_this_image, replace=False)
@@ -112,7 +120,7 @@ def _sample_rois(all_rois, gt_boxes, fg_rois_per_image, rois_per_image, num_clas
         fg_inds_ = npr.choice(fg_inds, size=fg_rois_per_image - fg_inds.size, replace=True)
         fg_inds = np.hstack((fg_inds_, fg_inds))
     if len(bg_inds_) == 0 and key == 'TRAIN':
-        _, bg_inds = _fg_bg_lists(max_overlaps, T.FG_THRESH, T.BG_THRESH_HI + 0.2, 0)
+        bg_inds = fb_buf[:cnt[2]].astype(np.int64)
     else:
         bg_inds = bg_inds_
     if len(bg_inds) == 0:
@@ -134,12 +142,10 @@ def _sample_rois(all_rois, gt_boxes, fg_rois_per_image, rois_per_image, num_clas
         p.inside_weights[i] = float(T.BBOX_INSIDE_WEIGHTS[i])
     rois = np.empty((K, 5), dtype=np.float32)
     labels = np.empty((K,), dtype=np.float32)
-    c4 = 4 * int(num_classes)
     bbox_targets = np.empty((K, c4), dtype=np.float32)
     inside = np.empty((K, c4), dtype=np.float32)
     outside = np.empty((K, c4), dtype=np.float32)
-    assign = np.ascontiguousarray(gt_assignment, dtype=np.int32)
-    _lib.check(lib.mxr_proposal_target_gather_host(
-        h.ptr, ctypes.byref(p), _lib.hptr(rois_f32), _lib.hptr(gt_f32), _lib.hptr(assign), _lib.hptr(keep_inds),
-        _lib.hptr(rois), _lib.hptr(labels), _lib.hptr(bbox_targets), _lib.hptr(inside), _lib.hptr(outside)))
+    _lib.check(lib.mxr_proposal_target_phase2_host(
+        h.ptr, ctypes.byref(p), _lib.hptr(keep_inds), _lib.hptr(rois), _lib.hptr(labels), _lib.hptr(bbox_targets),
+        _lib.hptr(inside), _lib.hptr(outside)))
     return labels, rois, bbox_targets, inside
