@@ -192,7 +192,9 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
   // 390 at the BASELINE configuration); later stripes and quota-less walks use the widest stripe
   int w0 = fz::kWMax, w1 = fz::kWMax;
   if (fa->max_keep > 0 && fa->max_keep < 360) {
-    w0 = round_up_int(fa->max_keep + fa->max_keep / 2 + 32, 32);
+    // 1.4 x the quota + 28: at the BASELINE configuration the 300th keep sits at sorted position 380 +- 11 (max 408 over
+    // 120 seeds), so 448 candidates settle the image in one stripe; when they do not, the next stripe carries on
+    w0 = round_up_int(fa->max_keep + (fa->max_keep * 2) / 5 + 28, 32);
     if (w0 > fz::kWMax) w0 = fz::kWMax;
     w1 = 256;
   }
