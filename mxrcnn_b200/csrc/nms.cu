@@ -1,6 +1,8 @@
 // helper/processing/nms.py:4-38 -- nms(dets, thresh), single and batched (per-class) forms.
 #include <string.h>
 
+#include <atomic>
+
 #include "nms_cluster.cuh"
 #include "nms_host.cuh"
 #include "sort.cuh"
@@ -371,8 +373,14 @@ const int kNoAllocMaxDevices = 64;
 // cudaGetSymbolAddress -- it is not a device address and must never be passed to a kernel.
 static __device__ __align__(256) unsigned char g_nms_noalloc_scratch[kNoAllocBytes];
 
-// Device address of g_nms_noalloc_scratch on each device, filled on first use.
-unsigned char* g_nms_noalloc_addr[kNoAllocMaxDevices];
+// Device address of g_nms_noalloc_scratch on each device, filled on first use (any host thread may be the first).
+std::atomic<unsigned char*> g_nms_noalloc_addr[kNoAllocMaxDevices];
+
+// n == 0: nothing to do but report it (no kernel of the pipeline is given a null pointer).
+__global__ void nms_noalloc_empty_kernel(int* nkeep) {
+  nkeep[0] = 0;
+  nkeep[1] = 0;
+}
 
 // First kernel of every call: the array still holds the previous call's data.
 __global__ void nms_noalloc_reset_kernel(unsigned char* zero_from, size_t zero_bytes, int* offsets, int n) {
@@ -389,7 +397,8 @@ int nms_noalloc_scratch(unsigned char** out, int* device_out) {
   int dev = -1;
   MXR_CUDA(cudaGetDevice(&dev));
   MXR_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, MXR_ERR_LIMIT, "mxr_nms_noalloc: device index %d not supported", dev);
-  if (g_nms_noalloc_addr[dev] == nullptr) {
+  unsigned char* known = g_nms_noalloc_addr[dev].load(std::memory_order_acquire);
+  if (known == nullptr) {
     // once per device, with that device current (it is: we just asked which one is)
     unsigned char* ptr = nullptr;
     cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_nms_noalloc_scratch);
@@ -397,9 +406,10 @@ int nms_noalloc_scratch(unsigned char** out, int* device_out) {
       set_error("mxr_nms_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
       return MXR_ERR_CUDA;
     }
-    g_nms_noalloc_addr[dev] = ptr;
+    g_nms_noalloc_addr[dev].store(ptr, std::memory_order_release);  // every thread computes the same address
+    known = ptr;
   }
-  *out = g_nms_noalloc_addr[dev];
+  *out = known;
   *device_out = dev;
   return MXR_OK;
 }
@@ -419,6 +429,11 @@ int mxr_nms_noalloc(void* stream, const void* dets, int n, int dtype, double thr
   unsigned char* scratch = nullptr;
   int dev = 0;
   MXR_TRY(nms_noalloc_scratch(&scratch, &dev));
+  if (n == 0) {
+    nms_noalloc_empty_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(nkeep_out);
+    MXR_CUDA(cudaGetLastError());
+    return MXR_OK;
+  }
   const size_t esize = dtype == MXR_DTYPE_F64 ? 8 : 4;
   NmsLayout L;
   make_layout(1, n, n, max_keep, esize, false, reinterpret_cast<char*>(scratch), &L);
@@ -428,9 +443,10 @@ int mxr_nms_noalloc(void* stream, const void* dets, int n, int dtype, double thr
   Handle tmp;  // plain host struct for the shared launch helpers: no workspace, profiling off
   memset(&tmp, 0, sizeof(tmp));
   tmp.device = dev;
-  int no_opt_in[8] = {0, 1 << 30, 1 << 30, 0, 0, 0, 0, 0};  // <= 24 KiB of dynamic smem here: no opt-in needed
+  int no_opt_in[12] = {0, 1 << 30, 1 << 30, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // <= 24 KiB of dynamic smem here: no opt-in needed
   tmp.smem_attr = no_opt_in;
   nms_noalloc_reset_kernel<<<4, 256, 0, s>>>(reinterpret_cast<unsigned char*>(L.ctrl), L.zero_bytes, L.offsets, n);
+  MXR_CUDA(cudaGetLastError());
   if (dtype == MXR_DTYPE_F64) {
     MXR_TRY(enqueue_t<double>(&tmp, s, L, reinterpret_cast<const double*>(dets), thresh, max_keep, keep_out, nkeep_out));
   } else {
