@@ -136,6 +136,7 @@ static int at_phase2(Handle* h, cudaStream_t s, AnchorTargetState* st, const int
                      double pos_w, double neg_w, const float* iw4, float* label, float* target, float* inside,
                      float* outside) {
   const AnchorTargetGeom& g = st->g;
+  MXR_TRY(ws_order(h, s));  // `s` may be the caller's stream: the next user of the workspace must wait for this work
   MXR_REQUIRE(n_fg >= 0 && n_bg >= 0 && n_fg + n_bg <= st->ranks_cap, MXR_ERR_INVALID,
               "mxr_anchor_target_phase2: bad disable counts %d/%d", n_fg, n_bg);
   if (n_fg + n_bg > 0) {

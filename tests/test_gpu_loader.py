@@ -44,3 +44,28 @@ def test_anchor_labels_device_equals_host_and_oracle(end2end):
         assert np.array_equal(host[2][i], want["bbox_inside_weight"][0])
         assert np.array_equal(host[3][i], want["bbox_outside_weight"][0])
         np.testing.assert_allclose(host[1][i], want["bbox_target"][0], rtol=2e-6, atol=1e-7)
+
+
+def test_anchor_labels_device_under_a_busy_stream():
+    """The per-image label kernels of the device path run on the trainer's (torch's current) stream while the next
+    image's first phase runs on the library's own stream; both use the handle's workspace.  With a backlog on the
+    trainer's stream the second image's phase 1 used to overwrite the scratch of the first image's pending phase 2
+    (ADVICE round 1).  The library now orders the streams; the batch must equal the host results regardless."""
+    import torch
+    from mxrcnn_b200.rcnn.loader import anchor_labels
+    feat = (1, 18, 38, 63)
+    gts = [synth.gt_boxes(170 + i, G=g) for i, g in enumerate((12, 3, 25, 7))]
+    infos = [np.array([[600, 1000, 1.6]], np.float32)] * 4
+    np.random.seed(9)
+    host = anchor_labels(feat, gts, infos)
+    a = torch.randn((4096, 4096), device="cuda:0")
+    for trial in range(3):
+        b = a
+        for _ in range(20):  # a few tens of milliseconds of queued work on the current stream
+            b = b @ a * 1e-3
+        np.random.seed(9)
+        dev = anchor_labels(feat, gts, infos, device="cuda:0")
+        torch.cuda.synchronize()
+        for h, d in zip(host[:4], dev[:4]):
+            assert np.array_equal(d.cpu().numpy(), h), trial
+        assert torch.isfinite(b).any() or True
