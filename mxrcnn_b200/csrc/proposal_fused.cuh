@@ -25,6 +25,9 @@
 namespace mxr {
 namespace fz {
 
+#ifndef FZ_PAIR_GROUP
+#define FZ_PAIR_GROUP 8  // pairs per unrolled group of the IoU block loop (compile-time bit positions)
+#endif
 #ifndef FZ_P1_GROUP
 #define FZ_P1_GROUP 4  // anchors per decode round (loads first, then arithmetic)
 #endif
@@ -179,15 +182,15 @@ __device__ __forceinline__ float pair_d(const Box32& r, const float4 cb, const f
 }
 __device__ __forceinline__ void block_bits(const Box32& r, const float4* __restrict__ cb, const float2* __restrict__ ca, int jn,
                                            u32& supp_out, u32& und_out) {
-  // groups of eight columns with compile-time bit positions; columns at and beyond jn (garbage inside the staging
+  // groups of FZ_PAIR_GROUP columns with compile-time bit positions; columns at and beyond jn (garbage inside the staging
   // arrays, which are kWMax long) are masked off by the caller
   u32 supp = 0;
   bool any_und = false;
 #pragma unroll 1
-  for (int j0 = 0; j0 < jn; j0 += 8) {
+  for (int j0 = 0; j0 < jn; j0 += FZ_PAIR_GROUP) {
     u32 s8 = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < FZ_PAIR_GROUP; ++j) {
       float tol;
       const float d = pair_d(r, cb[j0 + j], ca[j0 + j], &tol);
       s8 |= d > tol ? (1u << j) : 0u;

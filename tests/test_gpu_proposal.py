@@ -344,3 +344,55 @@ def test_stage_full_sorted_order(cfgname, seed):
     assert np.array_equal(out["anchor_index"][0, :n], st["keep_anchor_index"][:n])
     assert np.array_equal(out["keep"][0, :n], st["keep"][:n])
     assert np.array_equal(np.asarray(st["order"])[st["keep"][:n]], st["keep_anchor_index"][:n])
+
+
+def _adversarial(kind, seed, cfgname):
+    cfg = dict(synth.CONFIGS[cfgname])
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    rs = np.random.RandomState(seed + 7)
+    if kind == "wild_deltas":      # boxes far outside the image, clipped onto its border: exact duplicates, huge exp()
+        box = (box * 10).astype(np.float32)
+    elif kind == "overflow":       # exp() overflows to inf for some anchors, deltas of 1e30 for others
+        flat = box.reshape(-1)
+        flat[rs.choice(flat.size, 200, replace=False)] = np.float32(95.0)
+        flat[rs.choice(flat.size, 50, replace=False)] = np.float32(1e30)
+        flat[rs.choice(flat.size, 50, replace=False)] = np.float32(-1e30)
+    elif kind == "zero_deltas":    # boxes are the anchors themselves: integer coordinates, sides EQUAL to the threshold
+        box[:] = 0
+        cfg["min_size"] = 184      # scale 1.0 below: anchors of side 184 sit exactly on `ws >= min_size` (proposal.py:117)
+        info = np.array([[cfg["im_info"][0], cfg["im_info"][1], 1.0]], dtype=np.float32)
+    elif kind == "tiny_image":     # everything is clipped into a 20x30 window: degenerate and identical boxes
+        info = np.array([[20, 30, 1.0]], dtype=np.float32)
+        cfg["min_size"] = 0
+    elif kind == "thr_one":
+        cfg["thresh"] = 1.0        # outside (0,1): the float32 screen is off, every pair takes the float64 test
+    elif kind == "thr_zero":
+        cfg["thresh"] = 0.0
+    return cls, box, info, cfg
+
+
+@pytest.mark.parametrize("kind", ["wild_deltas", "overflow", "zero_deltas", "tiny_image", "thr_one", "thr_zero"])
+def test_screens_agree_with_float64_on_adversarial_inputs(kind, monkeypatch):
+    """The fused kernel decides the min-size filter and the IoU test on float32 images of the boxes inside rigorous
+    error bounds and hands everything else to the reference's float64 arithmetic.  Inputs built to sit ON the
+    thresholds, to overflow, or to collapse onto identical boxes must give exactly what the float64-only kernel
+    (MXRCNN_B200_V1) and the oracle give."""
+    from mxrcnn_b200 import _lib
+    cfgname = "tiny" if kind in ("thr_one", "thr_zero") else "voc_test"
+    cls, box, info, cfg = _adversarial(kind, 300, cfgname)
+    new = run(cls, box, info, cfg, rng=np.random.RandomState(1))
+    monkeypatch.setenv("MXRCNN_B200_V1", "1")
+    h = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_V1")
+    old = run(cls, box, info, cfg, rng=np.random.RandomState(1), handle=h)
+    h.close()
+    for k in ("rois", "scores", "keep", "anchor_index", "nkeep"):
+        assert np.array_equal(new[k], old[k]), (kind, k)
+    if cfgname == "tiny" or kind in ("zero_deltas", "tiny_image"):
+        with np.errstate(all="ignore"):
+            st = restate.proposal_stages(cls, box, info, cfg["feat_stride"], cfg["scales"], cfg["ratios"], False, cfg["pre"],
+                                         cfg["post"], cfg["thresh"], cfg["min_size"], rng=np.random.RandomState(1))
+        n = st["nkeep"]
+        assert int(new["nkeep"][0]) == n
+        assert np.array_equal(new["anchor_index"][0, :n], st["keep_anchor_index"][:n])
