@@ -94,7 +94,7 @@ struct Handle {
   // Both point into the process-wide table of this handle's DEVICE (api.cu): kernel attributes belong to
   // (kernel, device), not to a handle, so two handles must not cache them separately.
   int* smem_attr;     // [12] largest dynamic-smem opt-in already set per kernel (1 prep f32, 2 prep f64, 3 coop,
-                      // 4/5 first-generation fused proposal, 6/7 cluster NMS, 8/9 fused proposal); raise it through
+                      // 4/5 first-generation fused proposal, 6/7 cluster NMS, 8/9 fused proposal, 10/11 fused NMS); raise it through
                       // raise_dyn_smem() only
   int* coop_grid;     // [4] [0] co-resident grid of the cooperative NMS kernel (0: not queried)
   int* cluster_cap;   // [4][8] fused proposal kernels (first generation 4 / 12 keys per thread, second generation 4 / 12)

@@ -4,6 +4,7 @@
 #include <atomic>
 
 #include "nms_cluster.cuh"
+#include "nms_fused.cuh"
 #include "nms_host.cuh"
 #include "sort.cuh"
 
@@ -96,6 +97,8 @@ struct NmsLayout {
   void* area;
   int* orig;
   int* kept_slot;
+  float4* kbox;  // fused kernel: kept boxes as the float32 screen sees them
+  float4* kaux;
   u64* M;
   u64* g_sort_keys;
   u32* g_sort_pl;
@@ -106,7 +109,8 @@ struct NmsLayout {
   size_t total;
 };
 
-void make_layout(int P, int n_max, int n_total, int max_keep, size_t esize, bool host_io, char* base, NmsLayout* L) {
+void make_layout(int P, int n_max, int n_total, int max_keep, size_t esize, bool host_io, char* base, NmsLayout* L,
+                 bool fused = true) {
   L->P = P;
   L->n_max = n_max;
   L->cap = round_up_int(n_max < 1 ? 1 : n_max, 64);
@@ -123,6 +127,8 @@ void make_layout(int P, int n_max, int n_total, int max_keep, size_t esize, bool
   L->area = c.take<char>((size_t)P * L->cap * esize);
   L->orig = c.take<int>((size_t)P * L->cap);
   L->kept_slot = c.take<int>((size_t)P * L->keep_cap);
+  L->kbox = fused ? c.take<float4>((size_t)P * L->keep_cap) : nullptr;  // mxr_nms_noalloc runs the striped kernels
+  L->kaux = fused ? c.take<float4>((size_t)P * L->keep_cap) : nullptr;
   L->M = c.take<u64>((size_t)P * L->plan.max_width * (L->plan.max_width / 64));
   if (!L->use_smem_sort) {
     L->g_sort_keys = c.take<u64>((size_t)P * L->n_pow2_max);
@@ -236,6 +242,63 @@ int enqueue_cluster_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* de
   return MXR_OK;
 }
 
+// One launch of fz::nms_fused_kernel (nms_fused.cuh): a cluster per problem, the stripe engine of the fused proposal kernel.
+template <typename T>
+int enqueue_fused_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets, double thresh, int max_keep,
+                    int32_t* keep_out, int32_t* nkeep_out) {
+  fz::NmsFusedArgs<T> g;
+  g.dets = dets;
+  g.offsets = L.offsets;
+  g.box = reinterpret_cast<typename Ar<T>::Box*>(L.box);
+  g.area = reinterpret_cast<T*>(L.area);
+  g.orig = L.orig;
+  g.cap = L.cap;
+  g.kbox = L.kbox;
+  g.kaux = L.kaux;
+  g.keep_cap = L.keep_cap;
+  g.o.rois = nullptr;
+  g.o.scores = nullptr;
+  g.o.keep_pos = nullptr;
+  g.o.keep_orig = keep_out;
+  g.o.nkeep = nkeep_out;
+  g.o.rows = 0;
+  g.o.row_offsets = L.offsets;
+  g.ctrl = L.ctrl;
+  g.thr = (T)thresh;  // compared in the dtype of dets, like numpy (see enqueue_t)
+  g.max_keep = max_keep > 0 ? L.keep_cap : 0;
+  g.sort_cap = L.n_pow2_max < 1024 ? 1024 : L.n_pow2_max;
+  const size_t smem = fz::nms_fused_smem_bytes<T>(g.sort_cap);
+  const int slot = sizeof(T) == 8 ? 11 : 10;
+  MXR_TRY(raise_dyn_smem(h, slot, (const void*)fz::nms_fused_kernel<T>, smem, nullptr));
+  // Blocks of 32 x 32 pairs per stripe: up to 136 inside the stripe plus (kept / 32) x 16 against the kept list; the
+  // cluster shares them, the per-stripe resolve does not shrink with it.  Many problems: keep the whole grid resident.
+  // Measured (tools/nms_probe.py): one list of 2000 / 6000: 16 CTAs 61 / 239 us, 8 CTAs 68 / 286 us; eight lists of 6000:
+  // 8 CTAs 250 us, 16 CTAs 385 us (not all clusters resident); twenty lists of 300: 4 CTAs 28.6 us, 8 CTAs 39 us.
+  int csize = L.n_max > 1024 ? (L.P <= 4 ? 16 : 8) : (L.n_max > 256 ? 4 : 2);
+  while (csize > 2 && (long long)L.P * csize > 148) csize >>= 1;
+  if (h->cluster_override >= 2 && h->cluster_override <= 16) csize = h->cluster_override;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(csize, L.P);
+  cfg.blockDim = dim3(1024);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = csize;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (csize > 8)
+    MXR_CUDA(cudaFuncSetAttribute((const void*)fz::nms_fused_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  prof_begin(h, s, ST_NMS_CLUSTER);
+  MXR_CUDA(cudaLaunchKernelEx(&cfg, fz::nms_fused_kernel<T>, g));
+  prof_end(h, s);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
+}
+
 // offsets: HOST array of P+1 ints.
 int run(Handle* h, cudaStream_t s, const void* dets, bool dets_on_host, const int32_t* offsets, int P, int dtype,
         double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out) {
@@ -275,7 +338,13 @@ int run(Handle* h, cudaStream_t s, const void* dets, bool dets_on_host, const in
   }
   // one cluster launch when a problem's sort fits the leader's shared memory, else the striped kernels
   const bool use_cluster = !h->no_cluster && n_max <= (dtype == MXR_DTYPE_F64 ? 8192 : 16384);
-  if (dtype == MXR_DTYPE_F64) {
+  const bool use_fused = use_cluster && !h->use_v1 && P <= 65535;
+  if (use_fused) {
+    if (dtype == MXR_DTYPE_F64)
+      MXR_TRY(enqueue_fused_t<double>(h, s, L, reinterpret_cast<const double*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+    else
+      MXR_TRY(enqueue_fused_t<float>(h, s, L, reinterpret_cast<const float*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
+  } else if (dtype == MXR_DTYPE_F64) {
     if (use_cluster)
       MXR_TRY(enqueue_cluster_t<double>(h, s, L, reinterpret_cast<const double*>(d_dets), thresh, max_keep, d_keep, d_nkeep));
     else
@@ -436,7 +505,7 @@ int mxr_nms_noalloc(void* stream, const void* dets, int n, int dtype, double thr
   }
   const size_t esize = dtype == MXR_DTYPE_F64 ? 8 : 4;
   NmsLayout L;
-  make_layout(1, n, n, max_keep, esize, false, reinterpret_cast<char*>(scratch), &L);
+  make_layout(1, n, n, max_keep, esize, false, reinterpret_cast<char*>(scratch), &L, false);
   MXR_REQUIRE(L.total <= kNoAllocBytes, MXR_ERR_LIMIT, "mxr_nms_noalloc: layout of %zu bytes exceeds the %zu-byte scratch",
               L.total, kNoAllocBytes);
   cudaStream_t s = (cudaStream_t)stream;

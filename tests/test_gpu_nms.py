@@ -111,3 +111,59 @@ def test_nest_vs_reference_fixture_and_oracle():
         d = synth.class_dets(90 + n, n=n, dtype=dt, clusters=max(2, n // 30))
         assert nest(d, th) == restate.nest(d, th)
     assert nest(np.zeros((0, 5)), 0.9) == []
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_nms_fused_and_first_generation_cluster_kernels_agree(dtype, monkeypatch):
+    """nms_fused.cuh (float32 screen + exact test in the dtype of dets) against nms_cluster.cuh (every pair exact)."""
+    from mxrcnn_b200 import _lib
+    monkeypatch.setenv("MXRCNN_B200_V1", "1")
+    first = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_V1")
+    sized = {}
+    for c in (2, 4, 8, 16):
+        monkeypatch.setenv("MXRCNN_B200_CLUSTER", str(c))
+        sized[c] = _lib.Handle(0)
+    monkeypatch.delenv("MXRCNN_B200_CLUSTER")
+    for n, th in [(2, 0.5), (33, 0.3), (511, 0.5), (512, 0.5), (513, 0.5), (1024, 0.7), (1500, 0.3), (6000, 0.7)]:
+        dets = synth.class_dets(n + 11, n=n, dtype=dtype, clusters=max(2, n // 50))
+        want = [int(i) for i in restate.nms(dets, th)]
+        assert gpu_nms(dets, th) == want
+        assert gpu_nms(dets, th, handle=first) == want
+        for c, h in sized.items():
+            assert gpu_nms(dets, th, handle=h) == want, (n, c)
+            assert gpu_nms(dets, th, max_keep=37, handle=h) == want[:37], (n, c)
+    first.close()
+    for h in sized.values():
+        h.close()
+
+
+def _grid_dets(seed, n, dtype, shift=0.0, step=1.0):
+    """Boxes on an integer grid with few distinct sizes: many pairs whose IoU equals a simple fraction exactly."""
+    rs = np.random.RandomState(seed)
+    x1 = rs.randint(0, 40, n) * step + shift
+    y1 = rs.randint(0, 40, n) * step + shift
+    w = rs.choice([10, 20, 30, 40], n) * step
+    h = rs.choice([10, 20, 30, 40], n) * step
+    d = np.stack([x1, y1, x1 + w - 1, y1 + h - 1, rs.rand(n)], axis=1)
+    return d.astype(dtype)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_nms_screen_agrees_with_exact_arithmetic_on_adversarial_dets(dtype):
+    """Inputs chosen against the float32 screen of nms_fused.cuh: IoU exactly on the threshold, coordinates so large
+    that float32 cannot hold them (every pair goes to the exact test), tiny fractional sizes, thresholds 0 and 1."""
+    for th in (0.5, 1.0 / 3.0, 0.25, 0.2):
+        for seed in range(3):
+            dets = _grid_dets(seed, 700, dtype)
+            assert gpu_nms(dets, th) == [int(i) for i in restate.nms(dets, th)], (th, seed)
+    far = _grid_dets(5, 600, dtype, shift=3.0e6 if dtype == np.float64 else 6.0e5)
+    assert gpu_nms(far, 0.5) == [int(i) for i in restate.nms(far, 0.5)]
+    huge = _grid_dets(6, 300, dtype, shift=1.0e12, step=1.0e9)
+    assert gpu_nms(huge, 0.5) == [int(i) for i in restate.nms(huge, 0.5)]
+    small = _grid_dets(7, 600, dtype, shift=0.125, step=1.0 / 64.0)
+    assert gpu_nms(small, 0.5) == [int(i) for i in restate.nms(small, 0.5)]
+    frac = synth.class_dets(31, n=900, dtype=dtype, clusters=12)
+    frac[:, :4] = frac[:, :4] * dtype(1.0 / 3.0) + dtype(1000.1)
+    for th in (0.0, 0.3, 0.999, 1.0, 1.5, -0.5):
+        assert gpu_nms(frac, th) == [int(i) for i in restate.nms(frac, th)], th
