@@ -189,7 +189,7 @@ class ClockSampler(object):
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.first = index, [], None, 0
 
     def start(self):
         try:
@@ -205,6 +205,14 @@ class ClockSampler(object):
         for ln in self.proc.stdout:
             self.rows.append(ln.strip())
 
+    def mark(self):
+        self.first = len(self.rows)
+
+    def wait_first_row(self, timeout_s):
+        t0 = time.perf_counter()
+        while self.proc and not self.rows and time.perf_counter() - t0 < timeout_s:
+            time.sleep(0.01)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -215,7 +223,7 @@ class ClockSampler(object):
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for r in self.rows[self.first:]:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 9:
                 continue
@@ -474,6 +482,14 @@ def run_gpu_arm(args, rank, world, local_rank):
         return float(t.item())
 
     lib.mxr_reserve_proposal(h.ptr, ctypes.byref(p))
+    # The clock sampler (nvidia-smi -lms 100) is started here and samples through every timed region below.  Its process
+    # start-up and NVML initialisation take ~0.2 s of driver calls; a K = 20 timed region is 0.5 ms, so the sampler is
+    # given until its first row to settle instead of initialising on top of the timed launches.
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        sampler.wait_first_row(3.0)
+        sampler.mark()  # rows before this point were taken on an idle GPU: not part of the report
     # Pre-conditioning (un-timed, before the W warm-up steps): a fresh GPU idles at ~1.1 GHz and a timed region of
     # K = 20 steps lasts half a millisecond, so the same step is run for PRECONDITION_MS first to bring the clocks up.
     t_pre = time.perf_counter()
@@ -483,16 +499,14 @@ def run_gpu_arm(args, rank, world, local_rank):
             step(n_pre + i)
         n_pre += 50
         torch.cuda.synchronize(dev)
-    for i in range(warm):
-        step(i)
-    torch.cuda.synchronize(dev)
     assert int(nk[:, 0].min()) == post and int(nk[:, 1].max()) == 0, nk
     launches_per_step = h.last_launch_count()
+    # the W warm-up steps come last before the timed region: nothing else (no torch kernel of a check, no copy) runs
+    # between them and the first timed step
+    for i in range(warm):
+        step(i)
 
     # ---- timed region: device-resident inputs ----
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)

@@ -70,7 +70,9 @@ enum Stage {
   ST_CLUSTER = 11,
   ST_NMS_CLUSTER = 12,
   ST_BOX_HEAD = 13,
-  ST_COUNT = 14
+  ST_FUSED = 14,
+  ST_NMS_FUSED = 15,
+  ST_COUNT = 16
 };
 
 struct ProfRec {

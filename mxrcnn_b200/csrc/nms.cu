@@ -292,7 +292,7 @@ int enqueue_fused_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets
   cfg.numAttrs = 1;
   if (csize > 8)
     MXR_CUDA(cudaFuncSetAttribute((const void*)fz::nms_fused_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-  prof_begin(h, s, ST_NMS_CLUSTER);
+  prof_begin(h, s, ST_NMS_FUSED);
   MXR_CUDA(cudaLaunchKernelEx(&cfg, fz::nms_fused_kernel<T>, g));
   prof_end(h, s);
   MXR_CUDA(cudaGetLastError());

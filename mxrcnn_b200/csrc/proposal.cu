@@ -304,7 +304,7 @@ int enqueue_fused(Handle* h, cudaStream_t s, const mxr_proposal_params* p, const
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = (h->no_pdl || fa->pair_count) ? 1 : 2;
-  prof_begin(h, s, ST_CLUSTER);
+  prof_begin(h, s, ST_FUSED);
   MXR_CUDA(cudaLaunchKernelEx(&cfg, kern, *fa));
   prof_end(h, s);
   MXR_CUDA(cudaGetLastError());

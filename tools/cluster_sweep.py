@@ -38,7 +38,7 @@ def main():
                 call()
             prof = h.profile_read()
             h.profile_enable(False)
-            ms, cnt = prof["proposal_cluster_kernel"]
+            ms, cnt = prof.get("proposal_fused_kernel") or prof["proposal_cluster_kernel"]
             table[(cs, B)] = ms / cnt * 1e3
         h.close()
     print("| images per call | " + " | ".join("cluster %s" % ("auto" if s == "0" else s) for s in sizes) + " |  (us per call)")

@@ -38,7 +38,7 @@ def main():
                 call()
             prof = h.profile_read()
             h.profile_enable(False)
-            ms, cnt = prof["proposal_cluster_kernel"]
+            ms, cnt = prof.get("proposal_fused_kernel") or prof["proposal_cluster_kernel"]
             rows.setdefault(B, []).append(ms / cnt * 1e3)
         h.close()
     for B, (w, n) in sorted(rows.items()):
