@@ -284,6 +284,33 @@ __global__ void __launch_bounds__(1024, 1) proposal_fused_kernel(const __grid_co
   if (tid < 32) s_removed[tid] = 0u;
   if (tid < 16) s_rem[tid] = 0u;
   asm volatile("griddepcontrol.launch_dependents;");
+#ifndef FZ_NO_PREFETCH
+  // While this CTA waits for the previous kernel in the stream (programmatic dependent launch), it asks L2 for the slab
+  // of each input plane it is about to decode: the scores of the anchors rank * chunk ... and their four delta planes,
+  // at most two anchors' worth, i.e. ten contiguous pieces.  A prefetch has no architectural effect (L2 is the point
+  // of coherence: a producer kernel that is still writing these planes simply overwrites the prefetched lines), so it
+  // may run ahead of griddepcontrol.wait; the decode loop then finds its five loads per anchor in L2.
+  if (tid < 10) {
+    const DecodeGeom& dg0 = g.pg.g;
+    const int q_lo = rank * g.chunk, q_hi = min(q_lo + g.chunk, g.pg.n_crop);
+    if (q_lo < q_hi) {
+      const int a_lo = q_lo / g.hwc, a_hi = (q_hi - 1) / g.hwc;
+      const int piece = tid / 5, plane = tid - piece * 5;  // plane 0: score, 1..4: dx, dy, dw, dh
+      const int a = a_lo + piece;
+      if (a <= a_hi) {
+        const int r_lo = a == a_lo ? q_lo - a * g.hwc : 0, r_hi = a == a_hi ? q_hi - 1 - a * g.hwc : g.hwc - 1;
+        const int h_lo = r_lo / dg0.wc, h_hi = r_hi / dg0.wc;
+        const size_t first = (size_t)h_lo * dg0.W + (r_lo - h_lo * dg0.wc), last = (size_t)h_hi * dg0.W + (r_hi - h_hi * dg0.wc);
+        const float* base = plane == 0 ? g.cls_prob + (size_t)b * g.pg.cls_img_stride + g.pg.cls_fg_offset + (size_t)a * g.hw32
+                                       : g.bbox_pred + ((size_t)b * 4 * dg0.A + (size_t)a * 4 + (plane - 1)) * g.hw32;
+        // whole 16-byte units inside [first, last]: never a byte outside the planes this CTA reads anyway
+        const unsigned long long lo = ((unsigned long long)(base + first) + 15ull) & ~15ull;
+        const unsigned long long hi = (unsigned long long)(base + last + 1) & ~15ull;
+        if (hi > lo) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((unsigned)(hi - lo)) : "memory");
+      }
+    }
+  }
+#endif
   asm volatile("griddepcontrol.wait;" ::: "memory");
   if (g.null_run) return;  // launch + dependency floor of this configuration (tools/cluster_sweep2.py)
   s_bins[tid] = 0;  // kBins == blockDim.x
