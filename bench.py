@@ -404,6 +404,13 @@ def secondary_configs(lib, _lib, dev, peak_gbs, alu):
     gt64 = synth.gt_boxes(4, G=64)
     out["anchor_target"] = row("configs[2]: assign_anchor 38x63x9 anchors (8151 inside) x 64 gt, 256 sampled, fg 0.5",
                                lambda: assign_anchor((1, 18, 38, 63), gt64, info), 1121672, "rcnn/minibatch.py:204-395")
+    from mxrcnn_b200.rcnn.loader import anchor_labels
+    gts8 = [synth.gt_boxes(40 + i, G=g_) for i, g_ in enumerate((64, 6, 1, 40, 12, 3, 25, 7))]
+    infos8 = [info] * 8
+    out["anchor_target_batch8"] = row("loader hand-off: anchor_labels for 8 images (1..64 gt) into device batch tensors, "
+                                      "two launches per batch", lambda: anchor_labels((1, 18, 38, 63), gts8, infos8, device=dev),
+                                      8 * 1121672, "rcnn/loader.py:293-329 + rcnn/minibatch.py:204-395")
+    out["anchor_target_batch8"]["us_per_image"] = out["anchor_target_batch8"]["us_per_call_host_arrays"] / 8.0
     gt8 = synth.gt_boxes(5, G=8)
     allr = np.vstack((synth.jittered_rois(5, gt8, R=2000), np.hstack((np.zeros((8, 1), np.float32), gt8[:, :4]))))
     out["proposal_target"] = row("configs[3]: _sample_rois 2008 rois x 8 gt, 128 rois, fg 0.25, 21 classes",
@@ -791,7 +798,14 @@ def run_gpu_arm(args, rank, world, local_rank):
                         "float64_pairs_per_launch": counts["float64_pairs_per_launch"], "ops_per_pair": 15,
                         "full_triangle_pairs_per_launch": B * 17997000, "nms_phase_us": phases["nms_stripes"],
                         "peak_source": "mxr_bench_alu_peak (independent FADD/FMUL streams, -fmad=false)",
-                        "f64_peak_gops": alu["f64"], "frac_of_f64_peak": gops / alu["f64"]}
+                        "f64_peak_gops": alu["f64"], "frac_of_f64_peak": gops / alu["f64"],
+                        "note": "the stripes evaluate %.1f%% of the full triangle's pairs (windows of the score order are "
+                                "materialised only until post_nms_top_n boxes are kept); a lower pair count lowers this "
+                                "fraction and the step time together" % (100.0 * pairs / (B * 17997000.0))}
+            if sat:
+                # same pairs per image, whole step time of the saturating batch (all phases, not only the NMS stripes)
+                sat_gops = pairs / float(B) * sat["batch"] * 15 / (sat["ms_per_step"] * 1e-3) / 1e9
+                roof_alu["saturating_batch_frac_whole_step"] = sat_gops / alu["f32"]
         # issue-slot view: warp instructions per launch (from the committed ncu capture) over the step time against
         # 148 SMs x 4 schedulers x SM clock
         roof_issue = None

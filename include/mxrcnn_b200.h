@@ -286,6 +286,23 @@ int mxr_anchor_target_phase2(mxr_handle_t h, void* stream, const int32_t* fg_dis
                              const int32_t* bg_disable_ranks, int n_bg_disable, double positive_weight,
                              double negative_weight, const float* inside_weights4, float* label, float* bbox_target,
                              float* bbox_inside_weight, float* bbox_outside_weight);
+/* The same two phases for a BATCH of images that share the feature map (the loader pads the data first,
+ * rcnn/loader.py:283-286): one launch and one synchronisation per phase instead of one per image.
+ *   p: feat_*, num_anchors, feat_stride, allowed_border, overlaps thresholds, clobber (im_height / im_width / num_gt
+ *      are per image and ignored here);
+ *   im_heights_widths (n_images, 2): im_info[0][0], im_info[0][1] of every image;
+ *   gt_boxes (sum G, 5) f32, all images' boxes one after the other; gt_offsets (n_images + 1): image b owns rows
+ *      gt_offsets[b] .. gt_offsets[b+1];
+ *   counts_out (n_images, 3): n_inside, n_fg, n_bg.
+ * phase2: disable_ranks: image by image, the fg ranks then the bg ranks; disable_counts (n_images, 2);
+ *   weights (n_images, 2): positive, negative weight; outputs are the batch tensors label (n_images, A*H*W) and
+ *   bbox_target / inside / outside weights (n_images, 4A, H, W), device pointers, written on `stream`. */
+int mxr_anchor_target_batch_phase1(mxr_handle_t h, const mxr_anchor_target_params* p, const double* anchors, int n_images,
+                                   const float* im_heights_widths, const float* gt_boxes, const int32_t* gt_offsets,
+                                   int32_t* counts_out);
+int mxr_anchor_target_batch_phase2(mxr_handle_t h, void* stream, const int32_t* disable_ranks, const int32_t* disable_counts,
+                                   const double* weights, const float* inside_weights4, float* label, float* bbox_target,
+                                   float* bbox_inside_weight, float* bbox_outside_weight);
 int mxr_anchor_target_phase2_host(mxr_handle_t h, const int32_t* fg_disable_ranks, int n_fg_disable,
                                   const int32_t* bg_disable_ranks, int n_bg_disable, double positive_weight,
                                   double negative_weight, const float* inside_weights4, float* label,

@@ -111,6 +111,8 @@ SIGNATURES = {
     "mxr_anchor_target_phase1": (ctypes.c_int, [_VP, _VP, c_double_p, _VP, c_int_p]),
     "mxr_anchor_target_phase2": (ctypes.c_int, [_VP, _VP, c_int_p, ctypes.c_int, c_int_p, ctypes.c_int, ctypes.c_double,
                                                 ctypes.c_double, c_float_p, _VP, _VP, _VP, _VP]),
+    "mxr_anchor_target_batch_phase1": (ctypes.c_int, [_VP, _VP, c_double_p, ctypes.c_int, c_float_p, _VP, c_int_p, c_int_p]),
+    "mxr_anchor_target_batch_phase2": (ctypes.c_int, [_VP, _VP, c_int_p, c_int_p, c_double_p, c_float_p, _VP, _VP, _VP, _VP]),
     "mxr_anchor_target_phase2_host": (ctypes.c_int, [_VP, c_int_p, ctypes.c_int, c_int_p, ctypes.c_int, ctypes.c_double,
                                                      ctypes.c_double, c_float_p, _VP, _VP, _VP, _VP]),
     "mxr_fg_bg_lists": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double,
@@ -180,7 +182,7 @@ class Handle(object):
 
     def profile_read(self):
         """{kernel name: (total ms, launches)} since the last read; synchronises the device."""
-        n = 16
+        n = 32
         ms = (ctypes.c_double * n)()
         cnt = (ctypes.c_int32 * n)()
         check(load().mxr_profile_read(self._h, n, ms, cnt))

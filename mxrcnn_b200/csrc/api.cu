@@ -208,7 +208,7 @@ const char* mxr_profile_stage_name(int stage) {
                                         "nms_scan_kernel", "nms_prepare_kernel",   "boxes_kernels",    "overlaps_kernels",
                                         "anchor_target_kernels", "proposal_target_kernels", "nms_coop_kernel",
                                         "proposal_cluster_kernel", "nms_cluster_kernel", "box_head_kernel",
-                                        "proposal_fused_kernel", "nms_fused_kernel"};
+                                        "proposal_fused_kernel", "nms_fused_kernel", "anchor_phase2_kernel"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 

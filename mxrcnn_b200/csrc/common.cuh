@@ -72,7 +72,8 @@ enum Stage {
   ST_BOX_HEAD = 13,
   ST_FUSED = 14,
   ST_NMS_FUSED = 15,
-  ST_COUNT = 16
+  ST_ANCHOR_PHASE2 = 16,
+  ST_COUNT = 17
 };
 
 struct ProfRec {

@@ -1,5 +1,6 @@
 // Kernels of the training-target generators:
-//   assign_anchor         rcnn/minibatch.py:204-395          (anchor_* kernels)
+//   assign_anchor         rcnn/minibatch.py:204-395          (anchor_* kernels: phase 1 of maps too large for
+//                                                             anchor_fused.cuh, which holds the batched kernels)
 //   _sample_rois          rcnn/rpn/proposal_target.py:135-196 (fg_bg_lists_kernel, proposal_target_gather_kernel)
 //   sample_rois           rcnn/minibatch.py:151-201           (fg_bg_lists_kernel)
 // Random draws never happen here: the host layer draws from numpy's RNG in the reference's call
@@ -204,56 +205,6 @@ static __global__ void __launch_bounds__(1024) anchor_lists_kernel(AnchorTargetW
   if (threadIdx.x == 0) {
     w.counts[1] = nf;
     w.counts[2] = nb;
-  }
-}
-
-// labels[list[rank]] = -1 for the ranks the host drew (:321-325, :330-334).
-static __global__ void anchor_disable_kernel(AnchorTargetWs w, const int* __restrict__ fg_ranks, int n_fg, const int* __restrict__ bg_ranks,
-                                      int n_bg) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n_fg) w.labels[w.fg_list[fg_ranks[t]]] = -1.f;
-  else if (t < n_fg + n_bg) w.labels[w.bg_list[bg_ranks[t - n_fg]]] = -1.f;
-}
-
-// minibatch.py:336-385: targets for every inside anchor, weights, _unmap to all N anchors and the
-// NCHW transposes, written directly in the output layouts.  One thread per output anchor (a,h,w).
-static __global__ void __launch_bounds__(256) anchor_output_kernel(AnchorTargetGeom g, AnchorTargetWs w, const float* __restrict__ gt,
-                                                            float4 inside_w, float pos_w, float neg_w, float* __restrict__ label,
-                                                            float* __restrict__ target, float* __restrict__ inside,
-                                                            float* __restrict__ outside) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= g.N) return;
-  const int hw = g.fh * g.fw;
-  const int a = t / hw, cell = t - a * hw;
-  const int p = cell * g.A + a;
-  const int r = w.inside_rank[p];
-  float lab = -1.f;
-  float tg[4] = {0.f, 0.f, 0.f, 0.f}, iw[4] = {0.f, 0.f, 0.f, 0.f}, ow[4] = {0.f, 0.f, 0.f, 0.f};
-  if (r >= 0) {
-    lab = w.labels[r];
-    if (g.G > 0) {
-      const double* e = w.anchors_in + (size_t)r * 4;
-      const float* q = gt + (size_t)w.argmax[r] * 5;   // gt_boxes[argmax_overlaps, :4] stays float32 (:338)
-      double o[4];
-      bbox_transform_one<double, float, double>(e[0], e[1], e[2], e[3], q[0], q[1], q[2], q[3], o);
-      for (int k = 0; k < 4; ++k) tg[k] = (float)o[k];
-    }
-    if (lab == 1.f) {
-      iw[0] = inside_w.x;
-      iw[1] = inside_w.y;
-      iw[2] = inside_w.z;
-      iw[3] = inside_w.w;
-      for (int k = 0; k < 4; ++k) ow[k] = pos_w;
-    } else if (lab == 0.f) {
-      for (int k = 0; k < 4; ++k) ow[k] = neg_w;
-    }
-  }
-  label[t] = lab;
-  for (int k = 0; k < 4; ++k) {
-    const size_t o = (size_t)(a * 4 + k) * hw + cell;
-    target[o] = tg[k];
-    inside[o] = iw[k];
-    outside[o] = ow[k];
   }
 }
 

@@ -39,9 +39,9 @@ def anchor_labels(feat_shape, gt_boxes_list, im_info_list, feat_stride=16, ancho
         import torch  # device tensors and streams come from the harness / trainer side
         out = [torch.empty((B, N), dtype=torch.float32, device=device)] + \
               [torch.empty((B, 4 * A, fh, fw), dtype=torch.float32, device=device) for _ in range(3)]
-        for i, (gt, info) in enumerate(zip(gt_boxes_list, im_info_list)):
-            minibatch.assign_anchor(feat_shape, gt, info, feat_stride, anchor_scales, anchor_ratios, allowed_border,
-                                    out={k: t[i:i + 1] for k, t in zip(LABEL_KEYS, out)})
+        # the whole batch in two launches (one cluster per image) and two synchronisations
+        minibatch.assign_anchor_batch(feat_shape, gt_boxes_list, im_info_list, dict(zip(LABEL_KEYS, out)), feat_stride,
+                                      anchor_scales, anchor_ratios, allowed_border)
     if config.END2END == 1:
         flat = [np.asarray(gt, dtype=np.float32).reshape(1, -1) for gt in gt_boxes_list]
         width = max(f.shape[1] for f in flat)

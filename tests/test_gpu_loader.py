@@ -69,3 +69,54 @@ def test_anchor_labels_device_under_a_busy_stream():
         for h, d in zip(host[:4], dev[:4]):
             assert np.array_equal(d.cpu().numpy(), h), trial
         assert torch.isfinite(b).any() or True
+
+
+def test_anchor_labels_batch_ragged_gt_counts_vs_oracle():
+    """The batched kernels (one cluster per image) on a batch whose images differ in everything per-image: no gt at
+    all, more gts than one 64-box round, a gt that touches no inside anchor (quirk Q4: its column maximum of 0 makes
+    every inside anchor positive), a smaller image inside the padded map."""
+    from mxrcnn_b200.rcnn.loader import anchor_labels
+    feat = (1, 18, 38, 63)
+    far = np.array([[5000, 5000, 5100, 5100, 1]], np.float32)
+    gts = [np.zeros((0, 5), np.float32), synth.gt_boxes(301, G=150), far, synth.gt_boxes(302, G=65),
+           synth.gt_boxes(303, G=7, im_h=480, im_w=640)]
+    infos = [np.array([[600, 1000, 1.6]], np.float32)] * 4 + [np.array([[480, 640, 1.0]], np.float32)]
+    np.random.seed(77)
+    dev = anchor_labels(feat, gts, infos, device="cuda:0")
+    state_after = np.random.get_state()[1].copy()
+    np.random.seed(77)
+    cfg = restate.default_config()
+    for i in range(len(gts)):
+        want = restate.assign_anchor(feat, gts[i], infos[i], rng=np.random, cfg=cfg)
+        assert np.array_equal(dev[0][i].cpu().numpy(), want["label"][0]), i
+        assert np.array_equal(dev[2][i].cpu().numpy(), want["bbox_inside_weight"][0]), i
+        assert np.array_equal(dev[3][i].cpu().numpy(), want["bbox_outside_weight"][0]), i
+        np.testing.assert_allclose(dev[1][i].cpu().numpy(), want["bbox_target"][0], rtol=2e-6, atol=1e-7)
+    assert np.array_equal(np.random.get_state()[1], state_after)
+
+
+def test_anchor_labels_fused_and_single_image_kernels_agree(monkeypatch):
+    """MXRCNN_B200_V1=1 selects the single-image kernels (the path of maps too large for one cluster) on a map the
+    batched kernels also take: both must write the same tensors."""
+    import torch
+    from mxrcnn_b200 import _lib
+    from mxrcnn_b200.rcnn import minibatch
+    feat = (1, 18, 38, 63)
+    gts = [synth.gt_boxes(400 + i, G=g) for i, g in enumerate((20, 64, 3))]
+    infos = [np.array([[600, 1000, 1.6]], np.float32)] * 3
+    outs = []
+    for v1 in ("1", "0"):
+        monkeypatch.setenv("MXRCNN_B200_V1", v1)
+        h = _lib.Handle(0)
+        monkeypatch.setattr(_lib, "handle_for", lambda handle, *arrays: h)
+        t = [torch.empty((3, 9 * 38 * 63), dtype=torch.float32, device="cuda:0")] + \
+            [torch.empty((3, 36, 38, 63), dtype=torch.float32, device="cuda:0") for _ in range(3)]
+        np.random.seed(12)
+        minibatch.assign_anchor_batch(feat, gts, infos, dict(zip(("label", "bbox_target", "bbox_inside_weight",
+                                                                  "bbox_outside_weight"), t)))
+        torch.cuda.synchronize()
+        outs.append([x.cpu().numpy() for x in t])
+        h.close()
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b)
+    assert (outs[0][0] == 1).sum() > 0
