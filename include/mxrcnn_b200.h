@@ -187,6 +187,9 @@ int mxr_nms_host(mxr_handle_t h, const void* dets, int n, int dtype, double thre
  * keep_out + offsets[c]; nkeep_out (n_problems, 2).  offsets: HOST (n_problems+1). */
 int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_t* offsets, int n_problems, int dtype,
                     double thresh, int max_keep, int32_t* keep_out, int32_t* nkeep_out);
+/* Same with HOST dets / keep_out / nkeep_out: one upload, one launch, one download. */
+int mxr_nms_batched_host(mxr_handle_t h, const void* dets, const int32_t* offsets, int n_problems, int dtype, double thresh,
+                         int max_keep, int32_t* keep_out, int32_t* nkeep_out);
 
 /* ---- helper/processing/nms.py:40-70  nest(dets, thresh) -------------- */
 /* keep_flag[i] = 0 when some other box j has inter(i,j)/area(i) > thresh, else 1; dets (n,5) f32|f64,

@@ -90,6 +90,8 @@ SIGNATURES = {
     "mxr_nms_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int, _VP, _VP]),
     "mxr_nms_batched": (ctypes.c_int, [_VP, _VP, _VP, c_int_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                        ctypes.c_int, _VP, _VP]),
+    "mxr_nms_batched_host": (ctypes.c_int, [_VP, _VP, c_int_p, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_int,
+                                            _VP, _VP]),
     "mxr_nest": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, _VP]),
     "mxr_nest_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, _VP]),
     "mxr_box_head": (ctypes.c_int, [_VP, _VP, ctypes.POINTER(BoxHeadParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -407,6 +407,14 @@ int mxr_nms_batched(mxr_handle_t hh, void* stream, const void* dets, const int32
              keep_out, nkeep_out);
 }
 
+int mxr_nms_batched_host(mxr_handle_t hh, const void* dets, const int32_t* offsets, int n_problems, int dtype, double thresh,
+                         int max_keep, int32_t* keep_out, int32_t* nkeep_out) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_nms_batched_host: NULL handle");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_DEVICE(h);
+  return run(h, h->stream, dets, true, offsets, n_problems, dtype, thresh, max_keep, keep_out, nkeep_out);
+}
+
 }  // extern "C"
 
 // =========================================================================================

@@ -65,15 +65,12 @@ def nms_batched(dets_list, thresh, max_keep=0, handle=None):
     total = int(offsets[-1])
     if total == 0:
         return [[] for _ in arrs]
-    import torch  # the batched entry point takes device pointers; staging goes through torch here
-    dev = torch.device("cuda", h.device)
-    flat = torch.from_numpy(np.concatenate(arrs, axis=0)).to(dev)
-    keep = torch.empty((total,), dtype=torch.int32, device=dev)
-    nk = torch.zeros((len(arrs), 2), dtype=torch.int32, device=dev)
-    _lib.check(lib.mxr_nms_batched(h.ptr, _lib.current_stream_ptr(flat), flat.data_ptr(),
-                                   offsets.ctypes.data_as(_lib.c_int_p), len(arrs), 1 if dt == np.float64 else 0,
-                                   float(thresh), int(max_keep), keep.data_ptr(), nk.data_ptr()))
-    keep_h, nk_h = keep.cpu().numpy(), nk.cpu().numpy()
+    flat = np.ascontiguousarray(np.concatenate(arrs, axis=0))
+    keep_h = np.empty((total,), dtype=np.int32)
+    nk_h = np.zeros((len(arrs), 2), dtype=np.int32)
+    _lib.check(lib.mxr_nms_batched_host(h.ptr, _lib.hptr(flat), offsets.ctypes.data_as(_lib.c_int_p), len(arrs),
+                                        1 if dt == np.float64 else 0, float(thresh), int(max_keep), _lib.hptr(keep_h),
+                                        _lib.hptr(nk_h)))
     if (nk_h[:, 1] & 1).any():
         raise ValueError("nms: NaN in dets")
     return [[int(i) for i in keep_h[offsets[c]:offsets[c] + nk_h[c, 0]]] for c in range(len(arrs))]
