@@ -443,6 +443,10 @@ def run_gpu_arm(args, rank, world, local_rank):
         import torch.distributed as dist_mod
         dist = dist_mod
         dist.init_process_group("nccl", device_id=dev)
+        # barriers of the timed regions go through a host-side (gloo) group: an NCCL barrier is a GPU kernel, and a
+        # foreign kernel between the warm-up steps and the first timed step evicts this kernel's code from the
+        # instruction caches; the ranks are synchronised all the same
+        host_group = dist.new_group(backend="gloo")
     cfg = synth.CONFIGS[CONFIG]
     A = len(cfg["scales"]) * len(cfg["ratios"])
     B = BATCH
@@ -478,7 +482,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     def barrier():
         torch.cuda.synchronize(dev)
         if dist is not None:
-            dist.barrier()
+            dist.barrier(group=host_group)
         torch.cuda.synchronize(dev)
 
     def max_over_ranks(x):
