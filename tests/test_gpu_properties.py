@@ -82,3 +82,31 @@ def test_anchor_target_quotas_full_size():
         np.testing.assert_allclose(out["bbox_outside_weight"].sum(), 4.0 * n_ex * np.float32(1.0 / n_ex), rtol=1e-6)
         inw = out["bbox_inside_weight"].reshape(9, 4, 38, 63)
         assert np.array_equal(inw[:, 0] == 1, lab.reshape(9, 38, 63) == 1)
+
+
+@pytest.mark.parametrize("dtype,n", [(np.float32, 16384), (np.float64, 8192)])
+def test_nms_invariants_at_the_largest_single_launch_size(dtype, n):
+    """The longest list the fused NMS kernel takes (sort in the leader's shared memory), arithmetic in the dtype of
+    dets like numpy: kept boxes do not suppress each other, every dropped box has an earlier kept suppressor."""
+    from mxrcnn_b200.helper.processing.nms import nms
+    dets = synth.class_dets(91, n=n, dtype=dtype, clusters=n // 40)
+    dets[:, 4] = np.random.RandomState(91).permutation(n).astype(dtype) / dtype(n)   # distinct scores
+    thr = 0.5
+    keep = np.asarray(nms(dets, thr), dtype=np.int64)
+    order = np.argsort(-dets[:, 4], kind="stable")
+    pos = np.empty(n, np.int64)
+    pos[order] = np.arange(n)
+    assert np.all(np.diff(pos[keep]) > 0)                 # keep order = descending score
+    kept = dets[keep]
+    is_kept = np.zeros(n, bool)
+    is_kept[keep] = True
+    sup = np.zeros(n, bool)
+    t = dtype(thr)
+    for c0 in range(0, n, 2048):                          # (K, 2048) blocks of the IoU matrix
+        ov = _pair_ovr(kept[:, :4], dets[c0:c0 + 2048, :4])
+        assert ov.dtype == dtype
+        earlier = pos[keep][:, None] < pos[c0:c0 + 2048][None, :]
+        sup[c0:c0 + 2048] = ((ov > t) & earlier).any(axis=0)
+    assert not sup[is_kept].any(), "a kept box is suppressed by an earlier kept box"
+    assert sup[~is_kept].all(), "a dropped box has no earlier kept suppressor"
+    assert nms(kept, thr) == list(range(len(keep)))
