@@ -120,12 +120,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) anchor_phase1_kernel(const __gr
   cluster.sync();
   int n_inside = 0;
   {
-    int before = 0;
-    for (int t = 0; t < csize; ++t) {
-      const int v = *cluster.map_shared_rank(&s_tot[0], t);
-      before += t < rank ? v : 0;
-      n_inside += v;
-    }
+    // one remote read per lane (a cluster has at most 16 CTAs), then warp sums: one round trip instead of csize
+    const int v = lane < csize ? *cluster.map_shared_rank(&s_tot[0], lane) : 0;
+    const int before = __reduce_add_sync(0xffffffffu, lane < rank ? v : 0);
+    n_inside = __reduce_add_sync(0xffffffffu, v);
 #pragma unroll
     for (int k = 0; k < kAtItems; ++k) {
       if (k < g.items) {
@@ -314,14 +312,11 @@ __global__ void __launch_bounds__(kAtThreads, 1) anchor_phase1_kernel(const __gr
   }
   cluster.sync();
   {
-    int fbase = 0, bbase = 0, n_fg = 0, n_bg = 0;
-    for (int t = 0; t < csize; ++t) {
-      const int vf = *cluster.map_shared_rank(&s_tot[1], t), vb = *cluster.map_shared_rank(&s_tot[2], t);
-      fbase += t < rank ? vf : 0;
-      bbase += t < rank ? vb : 0;
-      n_fg += vf;
-      n_bg += vb;
-    }
+    const int vf = lane < csize ? *cluster.map_shared_rank(&s_tot[1], lane) : 0;
+    const int vb = lane < csize ? *cluster.map_shared_rank(&s_tot[2], lane) : 0;
+    const int fbase = __reduce_add_sync(0xffffffffu, lane < rank ? vf : 0);
+    const int bbase = __reduce_add_sync(0xffffffffu, lane < rank ? vb : 0);
+    const int n_fg = __reduce_add_sync(0xffffffffu, vf), n_bg = __reduce_add_sync(0xffffffffu, vb);
 #pragma unroll
     for (int k = 0; k < kAtItems; ++k) {
       if (lf[k] >= 0) w.fg_list[fbase + lf[k]] = rk[k];

@@ -77,10 +77,11 @@ int at_cluster_size(int N) {
   return 0;
 }
 
-int at_launch_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, const void* func, int csize, int B, cudaStream_t s) {
+int at_launch_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, const void* func, int csize, int B, cudaStream_t s,
+                  int threads = kAtThreads) {
   memset(cfg, 0, sizeof(*cfg));
   cfg->gridDim = dim3(csize, B);
-  cfg->blockDim = dim3(kAtThreads);
+  cfg->blockDim = dim3(threads);
   cfg->dynamicSmemBytes = 0;
   cfg->stream = s;
   attr[0].id = cudaLaunchAttributeClusterDimension;
