@@ -52,3 +52,31 @@ def test_box_head_oracle_cap_and_threshold_semantics():
     capped, _ = restate.box_head(rois, deltas, scores, shape, scale, max_per_image=max(1, total // 2))
     kept = np.concatenate([d[:, 4] for d in capped[1:]])
     assert len(kept) >= total // 2 and kept.min() >= np.sort(np.concatenate([d[:, 4] for d in dets[1:]]))[-max(1, total // 2)]
+
+
+def test_anchor_draws_consume_the_rng_like_the_reference_choice_calls():
+    """minibatch._anchor_draws hands the device RANKS: npr.choice(inds, size=k, replace=False) of the reference
+    (rcnn/minibatch.py:320-334) equals inds[npr.permutation(len(inds))[:k]] on the legacy global RandomState, draw for
+    draw.  Checked here for the quotas of the default configuration, RNG state included."""
+    from mxrcnn_b200.rcnn import minibatch
+    from mxrcnn_b200.rcnn.config import config
+    T = config.TRAIN
+    num_fg = int(T.RPN_FG_FRACTION * T.RPN_BATCH_SIZE)
+    for seed, (n_inside, n_fg, n_bg) in enumerate([(8151, 300, 7000), (8151, 20, 8000), (500, 129, 100), (40, 0, 40)]):
+        fg_inds = np.arange(n_fg) * 3 + 1                 # any index arrays of those lengths
+        bg_inds = np.arange(n_bg) * 2 + 5
+        np.random.seed(seed)
+        want_fg = np.random.choice(fg_inds, size=n_fg - num_fg, replace=False) if n_fg > num_fg else np.zeros((0,), int)
+        kept_fg = n_fg - want_fg.size
+        num_bg = T.RPN_BATCH_SIZE - kept_fg
+        want_bg = np.random.choice(bg_inds, size=n_bg - num_bg, replace=False) if n_bg > num_bg else np.zeros((0,), int)
+        state = np.random.get_state()[1].copy()
+        np.random.seed(seed)
+        fg_r, bg_r, pw, nw = minibatch._anchor_draws((n_inside, n_fg, n_bg), G=3)
+        assert np.array_equal(np.random.get_state()[1], state)
+        assert np.array_equal(fg_inds[fg_r], want_fg) and np.array_equal(bg_inds[bg_r], want_bg)
+        n_examples = kept_fg + (n_bg - want_bg.size)
+        assert pw == nw == 1.0 / n_examples
+    import pytest
+    with pytest.raises(ValueError):
+        minibatch._anchor_draws((0, 0, 0), G=2)          # the reference dies in argmax of an empty array
