@@ -191,6 +191,13 @@ int mxr_nms_batched(mxr_handle_t h, void* stream, const void* dets, const int32_
 int mxr_nms_batched_host(mxr_handle_t h, const void* dets, const int32_t* offsets, int n_problems, int dtype, double thresh,
                          int max_keep, int32_t* keep_out, int32_t* nkeep_out);
 
+/* ---- helper/dataset/imdb.py:153-170  the one-to-one matching loop of evaluate_recall ---- */
+/* boxes (n,4) f64 proposals, gt_boxes (k,4) f64, both HOST; covered_out (k) f64: round j's IoU -- the gt box with the best
+ * remaining cover (first maximum), matched to the proposal that covers it best (first maximum), both retired.  The IoU is
+ * bbox_overlaps' (helper/processing/bbox_regression.py:11-31) in float64; the (n,k) matrix is never materialised.
+ * A round with nothing left to match records -1 (the reference asserts on it). */
+int mxr_recall_cover_host(mxr_handle_t h, const double* boxes, int n, const double* gt_boxes, int k, double* covered_out);
+
 /* ---- helper/processing/nms.py:40-70  nest(dets, thresh) -------------- */
 /* keep_flag[i] = 0 when some other box j has inter(i,j)/area(i) > thresh, else 1; dets (n,5) f32|f64,
  * arithmetic in that dtype.  The kept list of the reference is the ascending indices with flag 1. */

@@ -117,6 +117,7 @@ SIGNATURES = {
     "mxr_anchor_target_batch_phase2": (ctypes.c_int, [_VP, _VP, c_int_p, c_int_p, c_double_p, c_float_p, _VP, _VP, _VP, _VP]),
     "mxr_anchor_target_phase2_host": (ctypes.c_int, [_VP, c_int_p, ctypes.c_int, c_int_p, ctypes.c_int, ctypes.c_double,
                                                      ctypes.c_double, c_float_p, _VP, _VP, _VP, _VP]),
+    "mxr_recall_cover_host": (ctypes.c_int, [_VP, c_double_p, ctypes.c_int, c_double_p, ctypes.c_int, c_double_p]),
     "mxr_fg_bg_lists": (ctypes.c_int, [_VP, _VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double,
                                        ctypes.c_double, _VP, _VP, _VP]),
     "mxr_fg_bg_lists_host": (ctypes.c_int, [_VP, _VP, ctypes.c_int, ctypes.c_int, ctypes.c_double, ctypes.c_double,

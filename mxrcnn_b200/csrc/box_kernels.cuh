@@ -187,4 +187,115 @@ static __global__ void __launch_bounds__(256) expand_targets_kernel(const float*
   }
 }
 
+
+// ---- one-to-one matching of proposals and gt boxes for the recall report (helper/dataset/imdb.py:153-170) ----
+// k rounds over the (n,k) IoU matrix of bbox_overlaps: take the gt with the best remaining cover
+// (overlaps.max(axis=0).argmax(): first maximum), the proposal that covers it best (overlaps[:, g].argmax(): first
+// maximum), record that IoU, retire both (their row / column become -1).  The matrix is never stored: each column keeps
+// its maximum over the live rows and the first row that attains it; after a round only the columns whose best row was
+// just retired are evaluated again.  One CTA; warp w owns the columns w, w + 32, ...
+struct RecallCoverArgs {
+  const double* boxes;  // (n,4)
+  int n;
+  const double* gt;     // (k,4)
+  int k;
+  double* col_max;      // (k) scratch
+  int* col_arg;         // (k) scratch
+  unsigned* row_dead;   // (ceil(n/32)) scratch, zeroed by the kernel
+  unsigned char* col_dead;  // (k) scratch
+  double* covered;      // (k) out
+};
+
+__device__ __forceinline__ void recall_column(const RecallCoverArgs& a, int g, int lane) {
+  const double qx1 = a.gt[(size_t)g * 4], qy1 = a.gt[(size_t)g * 4 + 1], qx2 = a.gt[(size_t)g * 4 + 2], qy2 = a.gt[(size_t)g * 4 + 3];
+  const double qarea = Ar<double>::mul(Ar<double>::add(Ar<double>::sub(qx2, qx1), 1.0), Ar<double>::add(Ar<double>::sub(qy2, qy1), 1.0));
+  double best = -1.0;  // a retired row reads -1 in the reference's matrix
+  int arg = 0x7fffffff;
+  for (int i = lane; i < a.n; i += 32) {
+    if ((a.row_dead[i >> 5] >> (i & 31)) & 1u) continue;
+    const double* b = a.boxes + (size_t)i * 4;
+    const double ov = overlap_one(b[0], b[1], b[2], b[3], qx1, qy1, qx2, qy2, qarea);
+    if (ov > best) {  // ascending i per lane: the first maximum of the lane
+      best = ov;
+      arg = i;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (ob > best || (ob == best && oa < arg)) {
+      best = ob;
+      arg = oa;
+    }
+  }
+  if (lane == 0) {
+    a.col_max[g] = best;
+    a.col_arg[g] = best < 0.0 ? 0 : arg;  // no live row left: argmax of a column of -1 is row 0
+  }
+}
+
+static __global__ void __launch_bounds__(1024) recall_cover_kernel(RecallCoverArgs a) {
+  __shared__ double s_val[32];
+  __shared__ int s_idx[32];
+  __shared__ int s_pick[2];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < (a.n + 31) / 32; i += blockDim.x) a.row_dead[i] = 0u;
+  for (int g = tid; g < a.k; g += blockDim.x) a.col_dead[g] = 0;
+  __syncthreads();
+  for (int g = warp; g < a.k; g += 32) recall_column(a, g, lane);
+  __syncthreads();
+  for (int j = 0; j < a.k; ++j) {
+    // g* = first column with the largest maximum (retired columns hold -1 and take part, like the reference's matrix)
+    double v = -2.0;
+    int gi = 0x7fffffff;
+    for (int g = tid; g < a.k; g += blockDim.x) {
+      const double c = a.col_max[g];
+      if (c > v) {
+        v = c;
+        gi = g;
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ov = __shfl_xor_sync(0xffffffffu, v, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, gi, o);
+      if (ov > v || (ov == v && oi < gi)) {
+        v = ov;
+        gi = oi;
+      }
+    }
+    if (lane == 0) {
+      s_val[warp] = v;
+      s_idx[warp] = gi;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      v = s_val[lane];
+      gi = s_idx[lane];
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, gi, o);
+        if (ov > v || (ov == v && oi < gi)) {
+          v = ov;
+          gi = oi;
+        }
+      }
+      if (lane == 0) {
+        const int b = a.col_arg[gi];
+        a.covered[j] = v;
+        s_pick[0] = gi;
+        s_pick[1] = b;
+        a.row_dead[b >> 5] |= 1u << (b & 31);  // overlaps[b, :] = -1
+        a.col_dead[gi] = 1;                    // overlaps[:, g] = -1
+        a.col_max[gi] = -1.0;
+        a.col_arg[gi] = 0;
+      }
+    }
+    __syncthreads();
+    const int b_star = s_pick[1];
+    for (int g = warp; g < a.k; g += 32)
+      if (!a.col_dead[g] && a.col_arg[g] == b_star) recall_column(a, g, lane);
+    __syncthreads();
+  }
+}
+
 }  // namespace mxr

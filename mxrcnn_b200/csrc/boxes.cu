@@ -231,6 +231,43 @@ int mxr_bbox_overlaps_host(mxr_handle_t hh, const double* boxes, int n, int box_
   return MXR_OK;
 }
 
+// ---- recall matching ---------------------------------------------------------------------
+int mxr_recall_cover_host(mxr_handle_t hh, const double* boxes, int n, const double* gt_boxes, int k, double* covered_out) {
+  MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_recall_cover_host: NULL handle");
+  MXR_REQUIRE(n >= 0 && k >= 0, MXR_ERR_INVALID, "mxr_recall_cover_host: bad shape");
+  if (k == 0) return MXR_OK;
+  MXR_REQUIRE(gt_boxes && covered_out && (n == 0 || boxes), MXR_ERR_INVALID, "mxr_recall_cover_host: NULL array");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_DEVICE(h);
+  Staged st(h);
+  MXR_TRY(ws_order(h, st.s));
+  const size_t ob = st.reserve((size_t)(n ? n : 1) * 32), og = st.reserve((size_t)k * 32);
+  const size_t om = st.reserve((size_t)k * 8), oa = st.reserve((size_t)k * 4), ord = st.reserve((size_t)(n / 32 + 1) * 4);
+  const size_t ocd = st.reserve((size_t)k), oc = st.reserve((size_t)k * 8);
+  MXR_TRY(ensure_device_ws(h, st.off));
+  char* w = h->d_ws;
+  if (n) MXR_CUDA(cudaMemcpyAsync(w + ob, boxes, (size_t)n * 32, cudaMemcpyHostToDevice, st.s));
+  MXR_CUDA(cudaMemcpyAsync(w + og, gt_boxes, (size_t)k * 32, cudaMemcpyHostToDevice, st.s));
+  RecallCoverArgs a;
+  a.boxes = reinterpret_cast<const double*>(w + ob);
+  a.n = n;
+  a.gt = reinterpret_cast<const double*>(w + og);
+  a.k = k;
+  a.col_max = reinterpret_cast<double*>(w + om);
+  a.col_arg = reinterpret_cast<int*>(w + oa);
+  a.row_dead = reinterpret_cast<unsigned*>(w + ord);
+  a.col_dead = reinterpret_cast<unsigned char*>(w + ocd);
+  a.covered = reinterpret_cast<double*>(w + oc);
+  h->last_launches = 0;
+  prof_begin(h, st.s, ST_OVERLAPS);
+  recall_cover_kernel<<<1, 1024, 0, st.s>>>(a);
+  prof_end(h, st.s);
+  MXR_CUDA(cudaGetLastError());
+  MXR_CUDA(cudaMemcpyAsync(covered_out, w + oc, (size_t)k * 8, cudaMemcpyDeviceToHost, st.s));
+  MXR_CUDA(cudaStreamSynchronize(st.s));
+  return MXR_OK;
+}
+
 // ---- expand_bbox_regression_targets ------------------------------------------------------
 int mxr_expand_bbox_targets(mxr_handle_t hh, void* stream, const float* data, int k, int num_classes,
                             const float* inside_weights4, float* targets, float* weights) {

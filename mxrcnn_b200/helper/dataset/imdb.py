@@ -42,6 +42,21 @@ def greedy_cover(overlaps):
     return covered
 
 
+def recall_cover(boxes, gt_boxes):
+    """``greedy_cover(bbox_overlaps(boxes, gt_boxes))`` in one launch, without the (n,k) matrix ever leaving the GPU
+    (or existing: every gt column keeps its best live proposal; imdb.py:149-170)."""
+    from ... import _lib
+    b = np.ascontiguousarray(np.asarray(boxes, dtype=np.float64)[:, :4])
+    q = np.ascontiguousarray(np.asarray(gt_boxes, dtype=np.float64)[:, :4])
+    covered = np.zeros((q.shape[0],), dtype=np.float64)
+    if q.shape[0]:
+        _lib.check(_lib.load().mxr_recall_cover_host(_lib.handle_for(None).ptr, b.ctypes.data_as(_lib.c_double_p), b.shape[0],
+                                                     q.ctypes.data_as(_lib.c_double_p), q.shape[0],
+                                                     covered.ctypes.data_as(_lib.c_double_p)))
+        assert (covered >= 0).all()   # imdb.py:165
+    return covered
+
+
 class RoidbOverlapMixin(object):
     """Needs ``self.num_images`` and ``self.num_classes`` like the reference's IMDB."""
 
@@ -75,7 +90,7 @@ class RoidbOverlapMixin(object):
                 continue
             if limit is not None:
                 boxes = boxes[:limit, :]
-            found.append(greedy_cover(bbox_overlaps(boxes.astype(np.float64), gt.astype(np.float64))))
+            found.append(recall_cover(boxes, gt))
         gt_overlaps = np.sort(np.concatenate(found)) if found else np.zeros(0)
         if thresholds is None:
             thresholds = np.arange(0.5, 0.95 + 1e-5, 0.05)

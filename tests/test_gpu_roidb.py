@@ -88,4 +88,30 @@ def test_compute_targets_and_cover_vs_oracle(seed):
         np.testing.assert_allclose(a[:, 3:], b[:, 3:], rtol=2e-6, atol=1e-7)
         m = bbox_overlaps(boxes.astype(np.float64), gt["boxes"].astype(np.float64))
         assert np.array_equal(greedy_cover(m), restate.recall_gt_overlaps(boxes, gt["boxes"]))
+        from mxrcnn_b200.helper.dataset.imdb import recall_cover
+        assert np.array_equal(recall_cover(boxes, gt["boxes"]), restate.recall_gt_overlaps(boxes, gt["boxes"]))
     assert class_overlaps(box_list[1], gt_roidb[1]["boxes"], gt_roidb[1]["gt_classes"], 21).sum() == 0  # image without gt
+
+
+def test_recall_cover_ties_many_gt_and_too_few_proposals():
+    """The matching kernel against the reference loop (imdb.py:153-170, restated in the oracle) where ties decide:
+    duplicated proposals and duplicated gt boxes (first maximum wins, by column then by row), integer-grid boxes whose
+    IoUs coincide, more gt boxes than one warp pass (700), and fewer proposals than gt boxes (the reference asserts)."""
+    from mxrcnn_b200.helper.dataset.imdb import recall_cover
+    rs = np.random.RandomState(3)
+
+    def grid(n, lo=0, hi=30):
+        x1 = rs.randint(lo, hi, n) * 8.0
+        y1 = rs.randint(lo, hi, n) * 8.0
+        w = rs.choice([16, 32, 64], n).astype(np.float64)
+        h = rs.choice([16, 32, 64], n).astype(np.float64)
+        return np.stack([x1, y1, x1 + w - 1, y1 + h - 1], axis=1)
+
+    for n, k in [(300, 40), (1500, 700), (64, 64), (5, 3)]:
+        boxes, gt = grid(n), grid(k)
+        boxes[n // 2:] = boxes[:n - n // 2]            # duplicated proposals
+        gt[k // 2:] = gt[:k - k // 2]                  # duplicated gt boxes
+        assert np.array_equal(recall_cover(boxes, gt), restate.recall_gt_overlaps(boxes, gt)), (n, k)
+    with pytest.raises(AssertionError):
+        recall_cover(grid(3), grid(5))
+    assert recall_cover(grid(4), np.zeros((0, 4))).shape == (0,)
