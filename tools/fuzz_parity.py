@@ -1,6 +1,6 @@
-"""Randomised parity sweep (not part of the test suite: minutes of oracle time): nms / nms_batched, assign_anchor batches
+"""Randomised parity sweep (not part of the test suite: minutes of oracle time): the proposal op, nms / nms_batched, assign_anchor batches
 and recall matching on random sizes, dtypes, thresholds and degenerate mixtures, each compared with oracle/restate.py.
-Usage: python tools/fuzz_parity.py [seconds per family, default 60]"""
+Usage: python tools/fuzz_parity.py [seconds per family, default 60] [proposal,nms,assign_anchor,recall]"""
 import os
 import sys
 import time
@@ -9,6 +9,59 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import restate, synth  # noqa: E402
+
+
+def fuzz_proposal(budget):
+    from mxrcnn_b200.helper.processing.generate_anchor import generate_anchors
+    from mxrcnn_b200.rcnn.rpn.proposal import proposal_forward
+    rs = np.random.RandomState(99)
+    t0, n_cases = time.time(), 0
+    while time.time() - t0 < budget:
+        H, W = int(rs.randint(3, 50)), int(rs.randint(3, 70))
+        scales = [(8, 16, 32), (4, 8, 16, 32), (16,)][rs.randint(3)]
+        ratios = [(0.5, 1, 2), (1,)][rs.randint(2)]
+        A = len(scales) * len(ratios)
+        N = A * H * W
+        pre = int(rs.choice([-1, 40, 300, 1000, 6000, 12000]))
+        post = int(rs.choice([1, 30, 300, 2000]))
+        thresh = float(rs.choice([0.3, 0.5, 0.7, 0.9]))
+        min_size = int(rs.choice([0, 16, 48]))
+        info_t = (H * 16 - int(rs.randint(0, 16)), W * 16 - int(rs.randint(0, 16)), float(rs.choice([1.0, 1.6, 0.6])))
+        seed = int(rs.randint(1 << 30))
+        cls, box, info = synth.proposal_inputs(seed, H=H, W=W, A=A, im_info=info_t)
+        kind = rs.randint(4)
+        fg = cls[0, A:].astype(np.float64)
+        if kind == 1:    # few distinct values: long tie runs, crowded buckets
+            fg = np.round(fg * rs.choice([6, 40, 300])) / rs.choice([6, 40, 300])
+        elif kind == 2:  # all scores inside a sliver of the range
+            fg = rs.choice([0.2, 0.7, 0.999]) + fg * rs.choice([1e-3, 3e-4, 0.05])
+        elif kind == 3:  # wild deltas
+            box = (box * np.float32(rs.choice([3.0, 8.0]))).astype(np.float32)
+        fg = np.clip(fg, 0, 1).astype(np.float32)
+        cls[0, A:] = fg
+        cls[0, :A] = 1 - fg
+        anchors = generate_anchors(16.0, list(ratios), np.array(scales, dtype=float))
+        try:
+            st = restate.proposal_stages(cls, box, info, 16, scales, ratios, False, pre, post, thresh, min_size,
+                                         rng=np.random.RandomState(seed), nms_stop_after=post)
+        except ValueError:  # nothing passes the min-size filter: the reference dies in npr.choice on an empty list
+            try:
+                proposal_forward(cls, box, info, anchors, 16, pre, post, thresh, min_size, rng=np.random.RandomState(seed))
+            except ValueError:
+                n_cases += 1
+                continue
+            raise AssertionError(("proposal: the oracle raised, the op did not", H, W, A, min_size, seed))
+        out = proposal_forward(cls, box, info, anchors, 16, pre, post, thresh, min_size, want_indices=True,
+                               rng=np.random.RandomState(seed))
+        n = int(out["nkeep"][0])
+        tag = ("proposal", H, W, A, pre, post, thresh, min_size, kind, seed)
+        assert n == st["nkeep"], tag
+        assert np.array_equal(out["keep"][0, :n], st["keep"][:n]), tag
+        assert np.array_equal(out["anchor_index"][0, :n], st["keep_anchor_index"][:n]), tag
+        assert np.array_equal(out["scores"][:n], st["scores"][:n]), tag
+        np.testing.assert_allclose(out["rois"][:n], st["rois"][:n], rtol=1e-5, atol=3e-4 * (8.0 if kind == 3 else 1.0))
+        n_cases += 1
+    return n_cases
 
 
 def fuzz_nms(budget):
@@ -102,5 +155,8 @@ def fuzz_recall(budget):
 
 if __name__ == "__main__":
     budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
-    for name, fn in (("nms", fuzz_nms), ("assign_anchor batches", fuzz_anchor), ("recall matching", fuzz_recall)):
-        print("%s: %d random cases equal to the oracle" % (name, fn(budget)), flush=True)
+    only = sys.argv[2].split(",") if len(sys.argv) > 2 else None
+    for name, fn in (("proposal", fuzz_proposal), ("nms", fuzz_nms), ("assign_anchor batches", fuzz_anchor),
+                     ("recall matching", fuzz_recall)):
+        if only is None or name.split()[0] in only:
+            print("%s: %d random cases equal to the oracle" % (name, fn(budget)), flush=True)
