@@ -274,8 +274,9 @@ int enqueue_fused_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets
   // cluster shares them, the per-stripe resolve does not shrink with it.  Many problems: keep the whole grid resident.
   // Measured (tools/nms_probe.py): one list of 2000 / 6000: 16 CTAs 61 / 239 us, 8 CTAs 68 / 286 us; eight lists of 6000:
   // 8 CTAs 250 us, 16 CTAs 385 us (not all clusters resident); twenty lists of 300: 4 CTAs 28.6 us, 8 CTAs 39 us.
-  int csize = L.n_max > 1024 ? (L.P <= 4 ? 16 : 8) : (L.n_max > 256 ? 4 : 2);
-  while (csize > 2 && (long long)L.P * csize > 148) csize >>= 1;
+  // eighty lists of 100: one CTA per list 24.7 us, two 32.5 us (ten blocks of pairs: nothing to share, no barrier to pay).
+  int csize = L.n_max > 1024 ? (L.P <= 4 ? 16 : 8) : (L.n_max > 256 ? 4 : (L.n_max > 128 ? 2 : 1));
+  while (csize > 2 && (long long)L.P * csize > 148) csize >>= 1;  // (never below two for the longer lists)
   if (h->cluster_override >= 2 && h->cluster_override <= 16) csize = h->cluster_override;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
