@@ -422,6 +422,20 @@ def secondary_configs(lib, _lib, dev, peak_gbs, alu):
     d2000 = synth.class_dets(77, n=2000)
     out["nms_2000"] = row("configs[4]: nms 0.3 over 2000 dets f64", lambda: nms(d2000, 0.3), 2000 * 40 + 2000 * 4,
                           "helper/processing/nms.py:4-38")
+    from mxrcnn_b200.helper.dataset.imdb import class_overlaps, recall_cover
+    from mxrcnn_b200.helper.processing.nms import nest
+    d300 = synth.class_dets(78, n=300)
+    out["nest_300"] = row("demo post-processing: nest(dets, 0.9) over 300 dets f64 (SURVEY 8f N2)", lambda: nest(d300, 0.9),
+                          300 * 40 + 300 * 4, "helper/processing/nms.py:40-70")
+    gt12 = synth.gt_boxes(6, G=12)
+    props = synth.jittered_rois(6, gt12, R=2000)[:, 1:5].astype(np.float64)
+    gcls = np.arange(12) % 20 + 1
+    out["roidb_overlaps_2000x12"] = row("offline roidb: best gt / IoU per proposal, 2000 proposals x 12 gt (SURVEY 8f N3)",
+                                        lambda: class_overlaps(props, gt12[:, :4], gcls, 21), 2000 * 32 + 12 * 32 + 2000 * 12,
+                                        "helper/dataset/imdb.py:45-55")
+    out["recall_cover_2000x12"] = row("evaluate_recall matching loop, 2000 proposals x 12 gt (SURVEY 8f N3)",
+                                      lambda: recall_cover(props, gt12[:, :4].astype(np.float64)), 2000 * 32 + 12 * 32 + 12 * 8,
+                                      "helper/dataset/imdb.py:153-170")
     r, d, sc, shp, scl = synth.box_head_inputs(7)
     out["box_head_300x21"] = row("test-time box head: 300 rois x 21 classes (bbox_pred, clip, threshold, per-class NMS, cap)",
                                  lambda: detections(sc, r, d, shp, scl), 300 * 21 * 4 + 300 * 16 + 300 * 80 * 4,

@@ -111,6 +111,15 @@ def test_nest_vs_reference_fixture_and_oracle():
         d = synth.class_dets(90 + n, n=n, dtype=dt, clusters=max(2, n // 30))
         assert nest(d, th) == restate.nest(d, th)
     assert nest(np.zeros((0, 5)), 0.9) == []
+    # inputs for which "no intersection" does not mean "keep": zero / negative areas, thresholds at and below zero
+    with np.errstate(divide="ignore", invalid="ignore"):
+        for dt in (np.float32, np.float64):
+            d = synth.class_dets(17, n=260, dtype=dt, clusters=9)
+            d[5, 2], d[9, 3] = d[5, 0] - 1, d[9, 1] - 1          # area 0
+            d[20, 2] = d[20, 0] - 7                              # negative area
+            d[40:50] = d[30:40]                                  # duplicates: contained in each other
+            for th in (0.9, 0.0, -0.5, 1.0):
+                assert nest(d, th) == restate.nest(d, th), (dt, th)
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
