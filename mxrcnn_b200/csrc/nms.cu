@@ -294,7 +294,15 @@ int enqueue_fused_t(Handle* h, cudaStream_t s, const NmsLayout& L, const T* dets
   if (csize > 8)
     MXR_CUDA(cudaFuncSetAttribute((const void*)fz::nms_fused_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   prof_begin(h, s, ST_NMS_FUSED);
-  MXR_CUDA(cudaLaunchKernelEx(&cfg, fz::nms_fused_kernel<T>, g));
+  cudaError_t le = cudaLaunchKernelEx(&cfg, fz::nms_fused_kernel<T>, g);
+  if (le != cudaSuccess && csize > 8) {
+    // a device (partition) that cannot host a 16-CTA cluster: the portable size does the same work
+    (void)cudaGetLastError();
+    cfg.gridDim = dim3(8, L.P);
+    attr[0].val.clusterDim.x = 8;
+    le = cudaLaunchKernelEx(&cfg, fz::nms_fused_kernel<T>, g);
+  }
+  MXR_CUDA(le);
   prof_end(h, s);
   MXR_CUDA(cudaGetLastError());
   return MXR_OK;

@@ -153,9 +153,18 @@ int at_phase1(Handle* h, const mxr_anchor_target_params* p, const double* anchor
     cudaLaunchAttribute attr[1];
     MXR_TRY(at_launch_cfg(&cfg, attr, (const void*)anchor_phase1_kernel, st->csize, B, s));
     prof_begin(h, s, ST_ANCHOR_TARGET);
-    MXR_CUDA(cudaLaunchKernelEx(&cfg, anchor_phase1_kernel, g, at, st->w));
-    prof_end(h, s);
-  } else {
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, anchor_phase1_kernel, g, at, st->w);
+    if (le != cudaSuccess && st->csize > 8) {
+      // a device (partition) that cannot host a 16-CTA cluster: the single-image kernels below take over
+      (void)cudaGetLastError();
+      st->csize = 0;
+      g.items = 0;
+    } else {
+      MXR_CUDA(le);
+      prof_end(h, s);
+    }
+  }
+  if (!st->csize) {
     // maps beyond one cluster's registers: the single-image kernels, image by image
     MXR_CUDA(cudaMemsetAsync(st->w.counts, 0, (char*)st->w.inside_rank - (char*)st->w.counts, s));  // counts, colmax
     for (int b = 0; b < B; ++b) {
