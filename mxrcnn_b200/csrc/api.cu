@@ -288,6 +288,7 @@ int mxr_proposal_pairs_read(mxr_handle_t hh, int max_images, uint32_t* pairs_out
 int mxr_synchronize(mxr_handle_t hh, void* stream) {
   MXR_REQUIRE(hh != nullptr, MXR_ERR_INVALID, "mxr_synchronize: NULL handle");
   Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_DEVICE(h);  // the stream belongs to the handle's device
   MXR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   return MXR_OK;
 }
