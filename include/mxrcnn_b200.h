@@ -171,6 +171,13 @@ int mxr_proposal_pad(mxr_handle_t h, void* stream, int image, int rows_per_image
  * (proposal.py:123-127), boxes kept, NaN flag].  Synchronises. */
 int mxr_decode_clip(mxr_handle_t h, void* stream, const mxr_proposal_params* p, const float* bbox_pred, const float* im_info,
                     const double* anchors, double* out_boxes, int32_t* out_valid);
+/* SURVEY 8b mxr_topk_sorted; rcnn/rpn/proposal.py:113-127: the complete pre-NMS candidate list of every image in
+ * processing order (min-size filter, descending score, pre_nms_top_n cut, ties as documented), as anchor rows
+ * (h*W + w)*A + a: out_order (B, out_capacity) int32 device, out_capacity >= min(pre_nms_top_n, A*hc*wc);
+ * out_count (B, 2) int32 device: list length, NaN flag.  nms_thresh / post_nms_top_n of `p` are ignored.  A stage for
+ * parity tests (it runs the op with a threshold nothing exceeds, on the float64 pair test: milliseconds). */
+int mxr_topk_sorted(mxr_handle_t h, void* stream, const mxr_proposal_params* p, const float* cls_prob, const float* bbox_pred,
+                    const float* im_info, const double* anchors, int out_capacity, int32_t* out_order, int32_t* out_count);
 int mxr_proposal_counts(mxr_handle_t h, int max_images, int32_t* counts_out, int32_t* images_out);
 
 /* ---- A5  helper/processing/nms.py:4-38  nms(dets, thresh) ---------------------------- */

@@ -71,6 +71,7 @@ SIGNATURES = {
     "mxr_proposal_count_pairs": (ctypes.c_int, [_VP, ctypes.c_int]),
     "mxr_proposal_pairs_read": (ctypes.c_int, [_VP, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), c_int_p]),
     "mxr_decode_clip": (ctypes.c_int, [_VP, _VP, ctypes.POINTER(ProposalParams), _VP, _VP, c_double_p, _VP, _VP]),
+    "mxr_topk_sorted": (ctypes.c_int, [_VP, _VP, ctypes.POINTER(ProposalParams), _VP, _VP, _VP, c_double_p, ctypes.c_int, _VP, _VP]),
     "mxr_proposal_counts": (ctypes.c_int, [_VP, ctypes.c_int, c_int_p, c_int_p]),
     "mxr_generate_anchors": (ctypes.c_int, [ctypes.c_double, c_double_p, ctypes.c_int, c_double_p, ctypes.c_int,
                                             c_double_p]),

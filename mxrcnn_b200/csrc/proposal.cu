@@ -546,6 +546,14 @@ __global__ void pad_rows_kernel(float* rois, float* scores, int row0, int nkeep,
   if (scores) scores[row0 + nkeep + first + t] = scores[row0 + sidx];
 }
 
+// mxr_topk_sorted: out_order[image][position in the pre-NMS list] = anchor row, from the walk-order outputs.
+__global__ void topk_unwalk_kernel(const int32_t* pos, const int32_t* rows, const int32_t* count, int per_image, int32_t* out_order) {
+  const int b = blockIdx.y, t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count[b * 2] || t >= per_image) return;
+  const int p = pos[(size_t)b * per_image + t];
+  if (p >= 0 && p < per_image) out_order[(size_t)b * per_image + p] = rows[(size_t)b * per_image + t];
+}
+
 }  // namespace
 
 extern "C" {
@@ -691,6 +699,39 @@ int mxr_proposal_forward_host(mxr_handle_t hh, const mxr_proposal_params* p, con
   MXR_REQUIRE(out_rois && out_nkeep, MXR_ERR_INVALID, "mxr_proposal_forward_host: NULL array argument");
   MXR_TRY(mxr_proposal_submit_host(hh, 0, p, cls_prob, bbox_pred, im_info, anchors, out_capacity));
   return mxr_proposal_wait_host(hh, 0, out_rois, out_scores, out_keep, out_anchor_index, out_nkeep);
+}
+
+// Stage entry (SURVEY 8b mxr_topk_sorted; rcnn/rpn/proposal.py:113-127): the complete pre-NMS list in processing order.
+// It is the op itself with a threshold nothing exceeds (an IoU is at most 1) and no post-NMS cut: every candidate is
+// "kept", so the anchor-index output is the ordered list the NMS walks.  The float32 screen is off at that threshold,
+// every pair takes the float64 test: milliseconds, a stage for tests, not for the hot path.
+int mxr_topk_sorted(mxr_handle_t hh, void* stream, const mxr_proposal_params* p, const float* cls_prob, const float* bbox_pred,
+                    const float* im_info, const double* anchors, int out_capacity, int32_t* out_order, int32_t* out_count) {
+  MXR_REQUIRE(hh != nullptr && p && cls_prob && bbox_pred && im_info && anchors && out_order && out_count, MXR_ERR_INVALID,
+              "mxr_topk_sorted: NULL argument");
+  Handle* h = reinterpret_cast<Handle*>(hh);
+  MXR_DEVICE(h);
+  mxr_proposal_params q = *p;
+  q.nms_thresh = 1.0;
+  q.post_nms_top_n = 0;
+  Layout L;
+  MXR_TRY(make_layout(&q, out_capacity, true, nullptr, &L));
+  MXR_REQUIRE(out_capacity >= L.n_max, MXR_ERR_INVALID, "mxr_topk_sorted: out_capacity %d < list length %d", out_capacity, L.n_max);
+  cudaStream_t s = (cudaStream_t)stream;
+  MXR_TRY(ws_order(h, s));
+  MXR_TRY(ensure_device_ws(h, L.total));
+  MXR_TRY(make_layout(&q, out_capacity, true, h->d_ws, &L));
+  const size_t hw = (size_t)L.H * L.W;
+  // everything goes to the layout's own output staging; the rows come out in the order the NMS walks them (nms.py:19
+  // re-sorts the list, which turns every run of equal scores around), next to their positions in the list itself:
+  // one scatter puts them back
+  int32_t* pos = reinterpret_cast<int32_t*>(L.d_out + L.off_keep);
+  int32_t* rows = reinterpret_cast<int32_t*>(L.d_out + L.off_anchor);
+  MXR_TRY(enqueue(h, s, &q, L, cls_prob, 2 * L.A * hw, L.A * hw, bbox_pred, im_info, anchors, reinterpret_cast<float*>(L.d_out),
+                  reinterpret_cast<float*>(L.d_out + L.off_scores), pos, rows, out_count));
+  topk_unwalk_kernel<<<dim3((L.out_rows + 255) / 256, L.B), 256, 0, s>>>(pos, rows, out_count, L.out_rows, out_order);
+  MXR_CUDA(cudaGetLastError());
+  return MXR_OK;
 }
 
 int mxr_decode_clip(mxr_handle_t hh, void* stream, const mxr_proposal_params* p, const float* bbox_pred, const float* im_info,

@@ -346,6 +346,44 @@ def test_stage_full_sorted_order(cfgname, seed):
     assert np.array_equal(np.asarray(st["order"])[st["keep"][:n]], st["keep_anchor_index"][:n])
 
 
+@pytest.mark.parametrize("cfgname,seed,ties", [("tiny", 121, False), ("voc_test", 122, False), ("voc_test", 123, True),
+                                               ("voc_train", 124, False), ("voc_alt", 125, False)])
+def test_stage_topk_sorted_is_the_oracles_order(cfgname, seed, ties):
+    """mxr_topk_sorted: the whole pre-NMS list -- every candidate, duplicates included -- in processing order
+    equals the oracle's ``order`` (proposal.py:113-127 with the documented tie rule), row for row."""
+    import ctypes
+    import torch
+    from mxrcnn_b200 import _lib
+    from mxrcnn_b200.helper.processing.generate_anchor import generate_anchors
+    cfg = synth.CONFIGS[cfgname]
+    A = len(cfg["scales"]) * len(cfg["ratios"])
+    cls, box, info = synth.proposal_inputs(seed, H=cfg["H"], W=cfg["W"], A=A, im_info=cfg["im_info"])
+    if ties:  # few distinct scores: the order inside a run of equal scores is the rule's, not the sort's
+        q = (np.round(cls[0, A:].astype(np.float64) * 500) / 500).astype(np.float32)
+        cls[0, A:] = q
+        cls[0, :A] = 1 - q
+    st = restate.proposal_stages(cls, box, info, cfg["feat_stride"], cfg["scales"], cfg["ratios"], False, cfg["pre"], 1,
+                                 cfg["thresh"], cfg["min_size"], nms_stop_after=1)
+    want = np.asarray(st["order"])
+    n_all = A * cfg["H"] * cfg["W"]
+    cap = min(cfg["pre"], n_all) if cfg["pre"] > 0 else n_all
+    anchors = generate_anchors(float(cfg["feat_stride"]), list(cfg["ratios"]), np.array(cfg["scales"], dtype=float))
+    p = _lib.ProposalParams(1, A, cfg["H"], cfg["W"], 0, 0, float(cfg["feat_stride"]), cfg["pre"], cfg["post"],
+                            cfg["thresh"], float(cfg["min_size"]), 0)
+    dev = torch.device("cuda:0")
+    cls_d, box_d, info_d = (torch.from_numpy(x).to(dev) for x in (cls, box, info))
+    order = torch.full((cap,), -7, dtype=torch.int32, device=dev)
+    cnt = torch.zeros((1, 2), dtype=torch.int32, device=dev)
+    h = _lib.Handle(0)
+    _lib.check(_lib.load().mxr_topk_sorted(h.ptr, int(torch.cuda.current_stream().cuda_stream), ctypes.byref(p),
+                                           cls_d.data_ptr(), box_d.data_ptr(), info_d.data_ptr(),
+                                           anchors.ctypes.data_as(_lib.c_double_p), cap, order.data_ptr(), cnt.data_ptr()))
+    torch.cuda.synchronize()
+    h.close()
+    assert int(cnt[0, 0]) == want.size and int(cnt[0, 1]) == 0
+    assert np.array_equal(order.cpu().numpy()[:want.size], want)
+
+
 def _adversarial(kind, seed, cfgname):
     cfg = dict(synth.CONFIGS[cfgname])
     A = len(cfg["scales"]) * len(cfg["ratios"])
