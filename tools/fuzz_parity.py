@@ -1,6 +1,6 @@
 """Randomised parity sweep (not part of the test suite: minutes of oracle time): the proposal op, nms / nms_batched, assign_anchor batches
 and recall matching on random sizes, dtypes, thresholds and degenerate mixtures, each compared with oracle/restate.py.
-Usage: python tools/fuzz_parity.py [seconds per family, default 60] [proposal,nms,assign_anchor,recall]"""
+Usage: python tools/fuzz_parity.py [seconds per family, default 60] [proposal,nms,assign_anchor,recall,nest]"""
 import os
 import sys
 import time
@@ -104,6 +104,25 @@ def fuzz_nms(budget):
     return n_cases
 
 
+def fuzz_nest(budget):
+    from mxrcnn_b200.helper.processing.nms import nest
+    rs = np.random.RandomState(11)
+    t0, n_cases = time.time(), 0
+    with np.errstate(divide="ignore", invalid="ignore"):
+        while time.time() - t0 < budget:
+            dt = np.float32 if rs.rand() < 0.5 else np.float64
+            n = int(rs.choice([1, 2, 33, 255, 256, 257, 600]))
+            d = synth.class_dets(int(rs.randint(1 << 30)), n=n, dtype=dt, clusters=max(2, n // 15))
+            if rs.rand() < 0.4 and n > 8:
+                d[n // 2:n // 2 + n // 8] = d[:n // 8]                      # duplicates
+                m = rs.rand(n) < 0.05
+                d[m, 2] = d[m, 0] - dt(rs.choice([1.0, 5.0]))               # zero / negative areas
+            th = float(rs.choice([0.9, 0.5, 0.99, 0.0, -0.25, 1.0]))
+            assert nest(d, th) == restate.nest(d, th), ("nest", dt, n, th)
+            n_cases += 1
+    return n_cases
+
+
 def fuzz_anchor(budget):
     from mxrcnn_b200.rcnn.loader import anchor_labels
     rs = np.random.RandomState(77)
@@ -157,6 +176,6 @@ if __name__ == "__main__":
     budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
     only = sys.argv[2].split(",") if len(sys.argv) > 2 else None
     for name, fn in (("proposal", fuzz_proposal), ("nms", fuzz_nms), ("assign_anchor batches", fuzz_anchor),
-                     ("recall matching", fuzz_recall)):
+                     ("recall matching", fuzz_recall), ("nest", fuzz_nest)):
         if only is None or name.split()[0] in only:
             print("%s: %d random cases equal to the oracle" % (name, fn(budget)), flush=True)
